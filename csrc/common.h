@@ -1,0 +1,76 @@
+// Internal declarations shared by store.cpp, runtime.cu and kernels.cu.
+#pragma once
+
+#include <stdarg.h>
+#include <stddef.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../include/pdcc.h"
+
+namespace pdcc {
+
+// thread-local error string behind pdcc_last_error()
+void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
+
+// ---- layout of one rank's symmetric block -------------------------------------------
+//
+//   [0, kCtrlBytes)                 ctrl   local-only bookkeeping (epochs, error record)
+//   [kCtrlBytes, kHeaderBytes)      pads   signal flags written by peers
+//   [kHeaderBytes, +rings)          rings  max_blocks x PDCC_RING_DEPTH tile slots
+//   [.., +heap_bytes)               heap   symmetric heap for zero-copy user tensors
+//
+// Every CTA index b owns ring b on every rank: slot(b, pos) sits at the same offset in
+// every rank's block, so one offset addresses "the same tile" on all peers and on the
+// multicast alias. A ring is only ever touched by CTAs with that index, which is what
+// lets per-CTA flag counters order every reuse of a slot across calls.
+constexpr size_t kCtrlBytes = 64 * 1024;
+constexpr int kNumChannels = 3;  // READY, MID, DONE
+constexpr size_t kPadBytes =
+    size_t(kNumChannels) * PDCC_MAX_BLOCKS * PDCC_MAX_RANKS * sizeof(uint32_t);
+constexpr size_t kHeaderBytes = 2 * 1024 * 1024;  // keeps rings 2 MiB aligned
+static_assert(kCtrlBytes + kPadBytes <= kHeaderBytes, "header too small");
+
+// ctrl words (uint32 index)
+constexpr int kCtrlErr = 0;        // first device-side timeout record: code
+constexpr int kCtrlErrInfo = 1;    // .. chan | tile | peer packed
+constexpr int kCtrlEpoch = 64;     // + b : tiles processed so far by CTA index b
+
+// What a kernel needs to know about the group, passed by value (88 bytes).
+struct DevComm {
+  int rank;
+  int nranks;
+  char* base[PDCC_MAX_RANKS];  // base[p] = local VA of rank p's symmetric block
+  char* mc;                    // multicast alias of the block (nullptr: no NVLS)
+  uint32_t slot_bytes;         // capacity of one tile slot
+  uint32_t timeout_ms;         // device-side wait budget
+};
+
+// One rank's view of one collective call.
+struct RankArgs {
+  DevComm comm;
+  const void* in;
+  void* out;
+  void* list[PDCC_MAX_RANKS];
+};
+
+struct Plan {
+  int algo;
+  int nblocks;
+  int threads;
+  uint64_t tile_bytes;  // payload bytes per CTA per tile (see kernels.cu)
+  int ntiles;
+};
+
+// kernels.cu
+// ring_limit: how many CTAs (= provisioned rings, capped by the SM count) a call may use.
+int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc_op_t& op,
+                    Plan* plan);
+// Launches one kernel covering `nlocal` ranks (1 = real multi-GPU rank, >1 = emulation:
+// cooperative launch with grid.y = nlocal, per-rank args read from the device array
+// dev_ranks). All ranks must describe the same collective.
+int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ranks,
+                      const pdcc_op_t& op, const Plan& plan, void* stream);
+size_t dtype_size(int dtype);
+
+}  // namespace pdcc

@@ -1,0 +1,310 @@
+// K8 — device-side primitives: system-scope loads/stores, NVLS multimem ops, the
+// per-CTA flag protocol (signal / wait with a wall-clock budget), and vector copy loops.
+//
+// Everything here is sm_100a PTX. Reference parity: the reference has no device code
+// (SURVEY.md §2.3); these replace what NCCL's kernels do under torch's ProcessGroupNCCL.
+#pragma once
+
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <stdint.h>
+
+#include "common.h"
+
+namespace pdcc {
+
+enum Chan : int { CH_READY = 0, CH_MID = 1, CH_DONE = 2 };
+
+// ---------------------------------------------------------------- memory ops ---------
+
+__device__ __forceinline__ uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void fence_acq_rel_sys() {
+  asm volatile("fence.acq_rel.sys;" ::: "memory");
+}
+
+// Data written by a peer (into my slot) or living on a peer: never serve it from L1.
+// Peer apertures are L1-cached / L2-bypassed on Blackwell (B300_MICROARCH.md, NVLink),
+// and a ring slot is re-read at the same address every PDCC_RING_DEPTH tiles.
+__device__ __forceinline__ uint4 ld_sys_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+// User tensors: read once, keep them out of L1.
+__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_v4(void* p, uint4 v) {
+  asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
+// NVLS: one store replicated by the switch into every bound device's block.
+__device__ __forceinline__ void multimem_st_v4(void* mc, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc),
+               "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+// NVLS: one load whose value is reduced inside the switch over every bound device.
+// KIND encodes type+op; only the combinations ptxas accepts for sm_100a exist
+// (no .mul at all, no min/max on .f32).
+enum MmKind : int {
+  MM_ADD_F32, MM_ADD_BF16, MM_ADD_F16, MM_ADD_F64,
+  MM_MIN_BF16, MM_MAX_BF16, MM_MIN_F16, MM_MAX_F16,
+  MM_ADD_S32, MM_MIN_S32, MM_MAX_S32, MM_MIN_S64, MM_MAX_S64, MM_ADD_U64,
+  MM_NONE
+};
+
+template <int KIND>
+__device__ __forceinline__ uint4 multimem_ld_reduce_v4(const void* mc) {
+  uint4 v;
+#define PDCC_MM_V4(INSTR)                                                                  \
+  asm volatile(INSTR " {%0,%1,%2,%3}, [%4];"                                               \
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)                                \
+               : "l"(mc)                                                                   \
+               : "memory")
+  if constexpr (KIND == MM_ADD_F32) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.add.v4.f32");
+  } else if constexpr (KIND == MM_ADD_BF16) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2");
+  } else if constexpr (KIND == MM_ADD_F16) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2");
+  } else if constexpr (KIND == MM_MIN_BF16) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.min.v4.bf16x2");
+  } else if constexpr (KIND == MM_MAX_BF16) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.max.v4.bf16x2");
+  } else if constexpr (KIND == MM_MIN_F16) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.min.v4.f16x2");
+  } else if constexpr (KIND == MM_MAX_F16) {
+    PDCC_MM_V4("multimem.ld_reduce.relaxed.sys.global.max.v4.f16x2");
+  } else if constexpr (KIND == MM_ADD_F64 || KIND == MM_MIN_S64 || KIND == MM_MAX_S64 ||
+                       KIND == MM_ADD_U64) {
+    // 64-bit forms have no .v4: two scalar loads cover the 16-byte unit.
+    uint64_t a, b;
+    const char* q = static_cast<const char*>(mc);
+#define PDCC_MM_S64(INSTR)                                                                 \
+  asm volatile(INSTR " %0, [%1];" : "=l"(a) : "l"(q) : "memory");                          \
+  asm volatile(INSTR " %0, [%1];" : "=l"(b) : "l"(q + 8) : "memory")
+    if constexpr (KIND == MM_ADD_F64) {
+      PDCC_MM_S64("multimem.ld_reduce.relaxed.sys.global.add.f64");
+    } else if constexpr (KIND == MM_MIN_S64) {
+      PDCC_MM_S64("multimem.ld_reduce.relaxed.sys.global.min.s64");
+    } else if constexpr (KIND == MM_MAX_S64) {
+      PDCC_MM_S64("multimem.ld_reduce.relaxed.sys.global.max.s64");
+    } else {
+      PDCC_MM_S64("multimem.ld_reduce.relaxed.sys.global.add.u64");
+    }
+#undef PDCC_MM_S64
+    v.x = static_cast<uint32_t>(a);
+    v.y = static_cast<uint32_t>(a >> 32);
+    v.z = static_cast<uint32_t>(b);
+    v.w = static_cast<uint32_t>(b >> 32);
+  } else {
+    // 32-bit integer forms have no .v4 either: four scalar loads.
+    const char* q = static_cast<const char*>(mc);
+#define PDCC_MM_S32(INSTR)                                                                 \
+  asm volatile(INSTR " %0, [%1];" : "=r"(v.x) : "l"(q) : "memory");                        \
+  asm volatile(INSTR " %0, [%1];" : "=r"(v.y) : "l"(q + 4) : "memory");                    \
+  asm volatile(INSTR " %0, [%1];" : "=r"(v.z) : "l"(q + 8) : "memory");                    \
+  asm volatile(INSTR " %0, [%1];" : "=r"(v.w) : "l"(q + 12) : "memory")
+    if constexpr (KIND == MM_ADD_S32) {
+      PDCC_MM_S32("multimem.ld_reduce.relaxed.sys.global.add.s32");
+    } else if constexpr (KIND == MM_MIN_S32) {
+      PDCC_MM_S32("multimem.ld_reduce.relaxed.sys.global.min.s32");
+    } else {
+      static_assert(KIND == MM_MAX_S32, "unknown multimem kind");
+      PDCC_MM_S32("multimem.ld_reduce.relaxed.sys.global.max.s32");
+    }
+#undef PDCC_MM_S32
+  }
+#undef PDCC_MM_V4
+  return v;
+}
+
+// ---------------------------------------------------------------- block context ------
+
+struct Ctx {
+  const RankArgs* a;
+  int rank, n;
+  int b;             // CTA index == ring index
+  uint32_t g0;       // tiles this ring had processed before this call
+  uint32_t* my_pad;  // flags peers write into my block
+  uint32_t* ctrl;
+  uint64_t deadline;  // globaltimer value after which waits give up
+  int* poisoned;      // smem: a wait already timed out in this CTA
+
+  __device__ __forceinline__ size_t slot_off(uint32_t g) const {
+    return kHeaderBytes +
+           (size_t(b) * PDCC_RING_DEPTH + (g % PDCC_RING_DEPTH)) * a->comm.slot_bytes;
+  }
+  __device__ __forceinline__ char* peer(int p, size_t off) const { return a->comm.base[p] + off; }
+  __device__ __forceinline__ char* mine(size_t off) const { return a->comm.base[rank] + off; }
+  __device__ __forceinline__ char* mc(size_t off) const { return a->comm.mc + off; }
+};
+
+__device__ __forceinline__ int flag_index(int chan, int b, int src) {
+  return (chan * PDCC_MAX_BLOCKS + b) * PDCC_MAX_RANKS + src;
+}
+
+// All threads call. Publishes everything this CTA wrote (locally, to peers, or through
+// the multicast alias) and then raises flag[chan][b][my rank] = val on every rank in mask.
+// bar.sync orders the other threads' writes before thread t's release (cumulativity).
+__device__ __forceinline__ void signal(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < c.n && ((mask >> t) & 1u)) {
+    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
+    st_release_sys(pad + flag_index(chan, c.b, c.rank), val);
+  }
+}
+
+// All threads call. Thread t waits for rank t's flag to reach val (wrap-safe), then a
+// system-scope fence makes it an acquire; bar.sync hands the guarantee to the whole CTA.
+// A wait that outlives the budget records an error and poisons the CTA instead of
+// hanging the GPU.
+__device__ __forceinline__ void wait(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+  const int t = threadIdx.x;
+  if (t < c.n && ((mask >> t) & 1u) && !*c.poisoned) {
+    const uint32_t* f = c.my_pad + flag_index(chan, c.b, t);
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_relaxed_sys(f) - val) < 0) {
+      if ((++spins & 0x3ffu) == 0 && globaltimer_ns() > c.deadline) {
+        if (atomicCAS(c.ctrl + kCtrlErr, 0u, 1u) == 0u)
+          c.ctrl[kCtrlErrInfo] = (uint32_t(chan) << 28) | (uint32_t(t) << 24) | (val & 0xffffffu);
+        *c.poisoned = 1;
+        break;
+      }
+    }
+    fence_acq_rel_sys();
+  }
+  __syncthreads();
+}
+
+// ---------------------------------------------------------------- copies -------------
+
+enum Ld : int { LD_USER = 0, LD_SYS = 1 };
+
+template <int LD>
+__device__ __forceinline__ uint4 ld16(const void* p) {
+  if constexpr (LD == LD_USER) return ld_stream_v4(p);
+  else return ld_sys_v4(p);
+}
+
+__device__ __forceinline__ bool aligned16(const void* p) {
+  return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
+
+// CTA-wide copy of n bytes. Fast path: both sides 16-byte aligned, UNROLL independent
+// 16-byte loads in flight per thread. Anything else degrades to 4- or 1-byte words;
+// that only happens for odd user views (arena-side addresses are always aligned).
+template <int LD, int UNROLL>
+__device__ __forceinline__ void copy_bytes(void* dst, const void* src, size_t n) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  char* d = static_cast<char*>(dst);
+  const char* s = static_cast<const char*>(src);
+  if (aligned16(d) && aligned16(s)) {
+    const size_t n16 = n >> 4;
+    for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
+      uint4 v[UNROLL];
+#pragma unroll
+      for (int k = 0; k < UNROLL; ++k) {
+        size_t j = i + size_t(k) * nt;
+        if (j < n16) v[k] = ld16<LD>(s + (j << 4));
+      }
+#pragma unroll
+      for (int k = 0; k < UNROLL; ++k) {
+        size_t j = i + size_t(k) * nt;
+        if (j < n16) st_v4(d + (j << 4), v[k]);
+      }
+    }
+    for (size_t i = (n16 << 4) + tid; i < n; i += nt) d[i] = s[i];
+  } else if (((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(s)) & 3u) == 0) {
+    const size_t n4 = n >> 2;
+    const uint32_t* s4 = reinterpret_cast<const uint32_t*>(s);
+    uint32_t* d4 = reinterpret_cast<uint32_t*>(d);
+    for (size_t i = tid; i < n4; i += nt) {
+      uint32_t v;
+      if constexpr (LD == LD_SYS) v = ld_relaxed_sys(s4 + i);
+      else v = s4[i];
+      d4[i] = v;
+    }
+    for (size_t i = (n4 << 2) + tid; i < n; i += nt) d[i] = s[i];
+  } else {
+    for (size_t i = tid; i < n; i += nt) {
+      if constexpr (LD == LD_SYS) d[i] = *reinterpret_cast<const volatile char*>(s + i);
+      else d[i] = s[i];
+    }
+  }
+}
+
+// CTA-wide push of n bytes from `src` into the same slot offset of every rank in `mask`
+// (P2P stores) or into the multicast alias (one multimem.st per 16 bytes). `src` must be
+// 16-byte aligned; n is rounded up to 16 (slots have room).
+template <int LD, int UNROLL>
+__device__ __forceinline__ void push_p2p(const Ctx& c, size_t off, const void* src, size_t n,
+                                         uint32_t mask) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const char* s = static_cast<const char*>(src);
+  const size_t n16 = (n + 15) >> 4;
+  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
+    uint4 v[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      size_t j = i + size_t(k) * nt;
+      if (j < n16) v[k] = ld16<LD>(s + (j << 4));
+    }
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      size_t j = i + size_t(k) * nt;
+      if (j < n16) {
+        for (int p = 0; p < c.n; ++p)
+          if ((mask >> p) & 1u) st_v4(c.peer(p, off) + (j << 4), v[k]);
+      }
+    }
+  }
+}
+
+template <int LD, int UNROLL>
+__device__ __forceinline__ void push_mc(const Ctx& c, size_t off, const void* src, size_t n) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const char* s = static_cast<const char*>(src);
+  const size_t n16 = (n + 15) >> 4;
+  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
+    uint4 v[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      size_t j = i + size_t(k) * nt;
+      if (j < n16) v[k] = ld16<LD>(s + (j << 4));
+    }
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      size_t j = i + size_t(k) * nt;
+      if (j < n16) multimem_st_v4(c.mc(off) + (j << 4), v[k]);
+    }
+  }
+}
+
+}  // namespace pdcc

@@ -1,0 +1,398 @@
+// Host side of the kernels: size -> (algorithm, grid, tile) planning, argument checks,
+// kernel selection and the launch itself (plain launch for a real rank, cooperative
+// launch with grid.y = nranks for the single-GPU emulation).
+//
+// The thresholds in plan_collective() are the measured size->variant table of
+// SURVEY.md §7.1 step 9; profiles/ holds the sweeps they were read from.
+#include <cuda_runtime.h>
+
+#include <atomic>
+
+#include "kernels.cuh"
+
+namespace pdcc {
+
+std::atomic<uint64_t> g_launches{0};
+
+size_t dtype_size(int dtype) {
+  switch (dtype) {
+    case PDCC_F32: case PDCC_I32: return 4;
+    case PDCC_BF16: case PDCC_F16: case PDCC_I16: return 2;
+    case PDCC_F64: case PDCC_I64: return 8;
+    case PDCC_U8: case PDCC_I8: return 1;
+    default: return 0;
+  }
+}
+
+// Can the switch do (dtype, op)?  Mirrors MmFor<> in reduce.cuh.
+static bool nvls_reducible(int dtype, int redop) {
+  if (redop == PDCC_PRODUCT) return false;
+  switch (dtype) {
+    case PDCC_F32: case PDCC_F64: return redop == PDCC_SUM;
+    case PDCC_BF16: case PDCC_F16: case PDCC_I32: case PDCC_I64: return true;
+    default: return false;
+  }
+}
+
+KernelFn reduce_kernel_for(int dtype, bool wide, int ar_algo, bool rooted) {
+  switch (dtype) {
+    case PDCC_F32: return reduce_table_f32(wide, ar_algo, rooted);
+    case PDCC_BF16: return reduce_table_bf16(wide, ar_algo, rooted);
+    case PDCC_F16: return reduce_table_f16(wide, ar_algo, rooted);
+    case PDCC_F64: return reduce_table_f64(wide, ar_algo, rooted);
+    case PDCC_I32: return reduce_table_i32(wide, ar_algo, rooted);
+    case PDCC_I64: return reduce_table_i64(wide, ar_algo, rooted);
+    case PDCC_U8: return reduce_table_u8(wide, ar_algo, rooted);
+    default: return nullptr;
+  }
+}
+
+static KernelFn move_kernel_for(int kind) {
+  switch (kind) {
+    case MV_BROADCAST_P2P: return move_kernel<MV_BROADCAST_P2P>;
+    case MV_BROADCAST_NVLS: return move_kernel<MV_BROADCAST_NVLS>;
+    case MV_SCATTER: return move_kernel<MV_SCATTER>;
+    case MV_GATHER: return move_kernel<MV_GATHER>;
+    case MV_ALLGATHER_PULL: return move_kernel<MV_ALLGATHER_PULL>;
+    case MV_ALLGATHER_NVLS: return move_kernel<MV_ALLGATHER_NVLS>;
+    case MV_BARRIER: return move_kernel<MV_BARRIER>;
+    default: return nullptr;
+  }
+}
+
+static uint64_t round_up(uint64_t v, uint64_t m) { return (v + m - 1) / m * m; }
+static uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+__device__ __forceinline__ uint64_t round_up_dev(uint64_t v, uint64_t m) { return (v + m - 1) / m * m; }
+__device__ __forceinline__ uint64_t ceil_div_dev(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && *v) ? atoi(v) : dflt;
+}
+
+int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc_op_t& op,
+                    Plan* plan) {
+  const int n = comm.nranks;
+  const size_t esz = dtype_size(op.dtype);
+  if (esz == 0) {
+    set_error("unsupported dtype %d", op.dtype);
+    return PDCC_EINVAL;
+  }
+  if (op.coll < 0 || op.coll >= PDCC_NUM_COLLS) {
+    set_error("unknown collective %d", op.coll);
+    return PDCC_EINVAL;
+  }
+  const uint64_t bytes = op.count * esz;
+  const bool is_reduce = op.coll == PDCC_ALL_REDUCE || op.coll == PDCC_REDUCE;
+  const int redop = op.redop == PDCC_AVG ? PDCC_SUM : op.redop;
+  if (is_reduce && !(redop == PDCC_SUM || redop == PDCC_PRODUCT || redop == PDCC_MIN ||
+                     redop == PDCC_MAX)) {
+    set_error("unsupported reduce op %d", op.redop);
+    return PDCC_EINVAL;
+  }
+
+  // ---- algorithm -----------------------------------------------------------------
+  int algo = op.algo;
+  const bool mc_ok = has_mc && comm.mc != nullptr;
+  if (op.coll == PDCC_ALL_REDUCE) {
+    const bool nvls = mc_ok && nvls_reducible(op.dtype, redop);
+    if (algo == PDCC_ALGO_AUTO) {
+      // One-shot moves N x bytes into every GPU but needs a single flag round; two-shot
+      // moves ~2 x bytes and needs two. Crossover measured on 8xB200 (profiles/).
+      const uint64_t oneshot_max = nvls ? uint64_t(env_int("PDCC_ONESHOT_NVLS_MAX", 64 << 10))
+                                        : uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10));
+      if (nvls) algo = bytes <= oneshot_max ? PDCC_ALGO_ONESHOT_NVLS : PDCC_ALGO_TWOSHOT_NVLS;
+      else algo = (bytes <= oneshot_max || n == 1) ? PDCC_ALGO_ONESHOT_P2P : PDCC_ALGO_TWOSHOT_P2P;
+    }
+    if ((algo == PDCC_ALGO_ONESHOT_NVLS || algo == PDCC_ALGO_TWOSHOT_NVLS) && !nvls) {
+      set_error("NVLS all_reduce not available for dtype %d op %d (multicast %s)", op.dtype,
+                redop, mc_ok ? "mapped" : "absent");
+      return PDCC_EUNSUPPORTED;
+    }
+    if (algo < PDCC_ALGO_ONESHOT_P2P || algo > PDCC_ALGO_TWOSHOT_NVLS) {
+      set_error("algo %d is not an all_reduce algorithm", algo);
+      return PDCC_EINVAL;
+    }
+  } else if (op.coll == PDCC_REDUCE) {
+    const bool nvls = mc_ok && nvls_reducible(op.dtype, redop);
+    if (algo == PDCC_ALGO_AUTO) algo = nvls ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
+    if (algo == PDCC_ALGO_ONESHOT_P2P) algo = PDCC_ALGO_P2P;
+    if (algo == PDCC_ALGO_ONESHOT_NVLS) algo = PDCC_ALGO_NVLS;
+    if (algo == PDCC_ALGO_NVLS && !nvls) {
+      set_error("NVLS reduce not available for dtype %d op %d", op.dtype, redop);
+      return PDCC_EUNSUPPORTED;
+    }
+    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS) {
+      set_error("algo %d is not a reduce algorithm", algo);
+      return PDCC_EINVAL;
+    }
+  } else if (op.coll == PDCC_BROADCAST || op.coll == PDCC_ALL_GATHER) {
+    if (algo == PDCC_ALGO_AUTO) {
+      if (op.coll == PDCC_BROADCAST) {
+        algo = (mc_ok && n > 2) ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
+      } else {
+        // pull is ingress-bound exactly like the multicast push and writes the user
+        // list directly (no copy-out); the push wins only while latency dominates.
+        algo = (mc_ok && bytes <= uint64_t(env_int("PDCC_AG_NVLS_MAX", 32 << 10))) ? PDCC_ALGO_NVLS
+                                                                                   : PDCC_ALGO_P2P;
+      }
+    }
+    if (algo == PDCC_ALGO_NVLS && !mc_ok) {
+      set_error("multicast not mapped for this comm");
+      return PDCC_EUNSUPPORTED;
+    }
+    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS) {
+      set_error("algo %d is not valid for collective %d", algo, op.coll);
+      return PDCC_EINVAL;
+    }
+  } else {
+    algo = PDCC_ALGO_P2P;
+  }
+
+  // ---- grid + tile ---------------------------------------------------------------
+  // cap: payload one CTA may place in one slot for this collective
+  uint64_t cap = comm.slot_bytes;
+  uint64_t align = 16;
+  const bool sub_slots = op.coll == PDCC_GATHER ||
+                         (op.coll == PDCC_ALL_GATHER && algo == PDCC_ALGO_NVLS);
+  if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);
+  if (op.coll == PDCC_ALL_REDUCE &&
+      (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS)) {
+    align = 16 * uint64_t(n);
+    cap = cap / align * align;
+  }
+  if (cap < align) {
+    set_error("slot_bytes %u too small for %d ranks", comm.slot_bytes, n);
+    return PDCC_EINVAL;
+  }
+
+  int max_blocks = env_int("PDCC_MAX_CTAS", 0);
+  if (ring_limit <= 0 || ring_limit > PDCC_MAX_BLOCKS) ring_limit = PDCC_MAX_BLOCKS;
+  if (max_blocks <= 0) {
+    // Bandwidth collectives: enough CTAs to keep ~4 MB in flight per GPU; the rooted
+    // movers are limited by one GPU's link so fewer suffice.
+    max_blocks = 64;
+  }
+  if (max_blocks > ring_limit) max_blocks = ring_limit;
+
+  int nb = op.nblocks;
+  if (nb <= 0) {
+    const uint64_t per_cta = 32 << 10;  // below this a CTA is latency- not bandwidth-bound
+    nb = int(ceil_div(bytes ? bytes : 1, per_cta));
+    if (nb > max_blocks) nb = max_blocks;
+    if (nb < 1) nb = 1;
+  }
+  if (nb > ring_limit) {
+    set_error("nblocks %d exceeds the %d provisioned rings", nb, ring_limit);
+    return PDCC_EINVAL;
+  }
+
+  uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
+  // aim for >= 4 tiles per CTA on big messages so staging overlaps the NVLink phase
+  uint64_t tile = per_cta / 4;
+  const uint64_t min_tile = 64 << 10;
+  if (tile < min_tile) tile = per_cta < min_tile ? per_cta : min_tile;
+  tile = round_up(tile, align);
+  if (tile > cap) tile = cap;
+  if (op.coll == PDCC_BARRIER) tile = align;
+
+  plan->algo = algo;
+  plan->nblocks = nb;
+  plan->threads = kThreads;
+  plan->tile_bytes = tile;
+  plan->ntiles = int(ceil_div(bytes ? bytes : 1, tile * uint64_t(nb)));
+  if (plan->ntiles < 1) plan->ntiles = 1;
+  return PDCC_OK;
+}
+
+int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ranks,
+                      const pdcc_op_t& op, const Plan& plan, void* stream) {
+  const DevComm& comm = ranks[0].comm;
+  const int n = comm.nranks;
+  const size_t esz = dtype_size(op.dtype);
+  const int redop = op.redop == PDCC_AVG ? PDCC_SUM : op.redop;
+
+  KArgs k{};
+  k.r = ranks[0];
+  k.emu = nullptr;
+  k.bytes = op.count * esz;
+  k.tile_bytes = plan.tile_bytes;
+  k.stride = uint32_t(round_up(plan.tile_bytes, 16));
+  k.ntiles = plan.ntiles;
+  k.root = op.root;
+  k.redop = redop;
+  k.scale = op.scale == 0.0f ? 1.0f : op.scale;
+  if (op.redop == PDCC_AVG) k.scale *= 1.0f / float(n);
+
+  if (op.root < 0 || op.root >= n) {
+    set_error("root %d out of range for %d ranks", op.root, n);
+    return PDCC_EINVAL;
+  }
+
+  KernelFn fn = nullptr;
+  switch (op.coll) {
+    case PDCC_ALL_REDUCE: {
+      const bool wide = op.out_dtype != op.dtype;
+      if (wide && !(op.out_dtype == PDCC_F32 && (op.dtype == PDCC_BF16 || op.dtype == PDCC_F16))) {
+        set_error("fused cast supports bf16/f16 -> f32 only");
+        return PDCC_EINVAL;
+      }
+      fn = reduce_kernel_for(op.dtype, wide, plan.algo - PDCC_ALGO_ONESHOT_P2P, false);
+      break;
+    }
+    case PDCC_REDUCE:
+      if (op.out_dtype != op.dtype) {
+        set_error("reduce has no fused cast");
+        return PDCC_EINVAL;
+      }
+      fn = reduce_kernel_for(op.dtype, false,
+                             plan.algo == PDCC_ALGO_NVLS ? AR_ONESHOT_NVLS : AR_ONESHOT_P2P, true);
+      break;
+    case PDCC_BROADCAST:
+      fn = move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_BROADCAST_NVLS : MV_BROADCAST_P2P);
+      break;
+    case PDCC_SCATTER: fn = move_kernel_for(MV_SCATTER); break;
+    case PDCC_GATHER: fn = move_kernel_for(MV_GATHER); break;
+    case PDCC_ALL_GATHER:
+      fn = move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_ALLGATHER_NVLS : MV_ALLGATHER_PULL);
+      break;
+    case PDCC_BARRIER: fn = move_kernel_for(MV_BARRIER); break;
+    default: break;
+  }
+  if (!fn) {
+    set_error("no kernel for collective %d dtype %d algo %d", op.coll, op.dtype, plan.algo);
+    return PDCC_EUNSUPPORTED;
+  }
+
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  cudaError_t err;
+  if (nlocal == 1) {
+    fn<<<dim3(plan.nblocks, 1, 1), dim3(plan.threads, 1, 1), 0, st>>>(k);
+    err = cudaGetLastError();
+  } else {
+    // Emulation: the per-rank args live in device memory (dev_ranks); all
+    // nlocal x nblocks CTAs wait on each other, so they must be co-resident, which is
+    // exactly what a cooperative launch guarantees (or refuses with an error).
+    k.emu = dev_ranks;
+    void* params[] = {&k};
+    err = cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(fn),
+                                      dim3(plan.nblocks, nlocal, 1), dim3(plan.threads, 1, 1),
+                                      params, 0, st);
+  }
+  if (err != cudaSuccess) {
+    set_error("kernel launch failed: %s", cudaGetErrorString(err));
+    return PDCC_ECUDA;
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return PDCC_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// K9 local helpers: the world-size-1 degenerate collectives (a list op over one rank is a
+// copy) and the DP demo's scale+cast when there is nobody to reduce with.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) local_copy_kernel(char* dst, const char* src,
+                                                              uint64_t bytes) {
+  // each CTA takes a contiguous span so its loads stream
+  const uint64_t per = round_up_dev(ceil_div_dev(bytes, gridDim.x), 16);
+  const uint64_t lo = per * blockIdx.x;
+  if (lo >= bytes) return;
+  const uint64_t len = bytes - lo < per ? bytes - lo : per;
+  copy_bytes<LD_USER, 8>(dst + lo, src + lo, len);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads) scale_cast_kernel(void* dst, const T* src,
+                                                              uint64_t count, float scale,
+                                                              bool wide) {
+  using Tr = Traits<T>;
+  const uint64_t n16 = (count + Tr::K - 1) / Tr::K;
+  const bool vec = aligned16(src);
+  for (uint64_t j = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; j < n16;
+       j += uint64_t(gridDim.x) * blockDim.x) {
+    const uint64_t e = j * Tr::K;
+    const int valid = count - e < uint64_t(Tr::K) ? int(count - e) : Tr::K;
+    Acc<T> acc;
+    if (vec && valid == Tr::K) {
+      acc.init(ld_stream_v4(src + e));
+    } else {
+      for (int i = 0; i < Tr::K; ++i) acc.v[i] = i < valid ? Tr::up(src[e + i]) : typename Tr::C(0);
+    }
+    acc.scale(scale);
+    if (wide) store_unit<T, true>(dst, e, acc, valid);
+    else store_unit<T, false>(dst, e, acc, valid);
+  }
+}
+
+}  // namespace pdcc
+
+using namespace pdcc;
+
+extern "C" {
+
+uint64_t pdcc_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+static int set_device_checked(int device) {
+  if (device < 0) return PDCC_OK;
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) {
+    set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    return PDCC_ECUDA;
+  }
+  return PDCC_OK;
+}
+
+int pdcc_local_copy(void* dst, const void* src, uint64_t bytes, int device, void* stream) {
+  if (bytes == 0 || dst == src) return PDCC_OK;
+  if (!dst || !src) return PDCC_EINVAL;
+  int rc = set_device_checked(device);
+  if (rc) return rc;
+  uint64_t blocks = (bytes + (64 << 10) - 1) / (64 << 10);
+  if (blocks > 4 * 148) blocks = 4 * 148;
+  local_copy_kernel<<<dim3(unsigned(blocks)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<char*>(dst), static_cast<const char*>(src), bytes);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("local_copy launch: %s", cudaGetErrorString(e));
+    return PDCC_ECUDA;
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return PDCC_OK;
+}
+
+int pdcc_local_scale_cast(void* dst, const void* src, uint64_t count, int dtype, int out_dtype,
+                          float scale, int device, void* stream) {
+  if (count == 0) return PDCC_OK;
+  if (!dst || !src) return PDCC_EINVAL;
+  const bool wide = out_dtype != dtype;
+  if (wide && !(out_dtype == PDCC_F32 && (dtype == PDCC_BF16 || dtype == PDCC_F16))) {
+    set_error("scale_cast supports bf16/f16 -> f32 only");
+    return PDCC_EINVAL;
+  }
+  int rc = set_device_checked(device);
+  if (rc) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t esz = dtype_size(dtype);
+  uint64_t units = (count * esz + 15) / 16;
+  uint64_t blocks = (units + kThreads - 1) / kThreads;
+  if (blocks > 8 * 148) blocks = 8 * 148;
+  dim3 g{unsigned(blocks)}, b{unsigned(kThreads)};
+  switch (dtype) {
+    case PDCC_F32: scale_cast_kernel<float><<<g, b, 0, st>>>(dst, static_cast<const float*>(src), count, scale, false); break;
+    case PDCC_BF16: scale_cast_kernel<__nv_bfloat16><<<g, b, 0, st>>>(dst, static_cast<const __nv_bfloat16*>(src), count, scale, wide); break;
+    case PDCC_F16: scale_cast_kernel<__half><<<g, b, 0, st>>>(dst, static_cast<const __half*>(src), count, scale, wide); break;
+    case PDCC_F64: scale_cast_kernel<double><<<g, b, 0, st>>>(dst, static_cast<const double*>(src), count, scale, false); break;
+    default:
+      set_error("scale_cast: unsupported dtype %d", dtype);
+      return PDCC_EINVAL;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("scale_cast launch: %s", cudaGetErrorString(e));
+    return PDCC_ECUDA;
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return PDCC_OK;
+}
+
+}  // extern "C"

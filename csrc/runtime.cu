@@ -1,0 +1,1063 @@
+// R2/R3/R4 — communicator runtime.
+//
+// Per group and per rank this file owns ONE physical "symmetric block" (ctrl words,
+// signal pads, tile rings, optional symmetric heap; layout in common.h), makes every
+// peer's block a plain device pointer in this process, and — where the box allows —
+// binds all blocks to one NVSwitch multicast object so that a single address reaches
+// every GPU (multimem.*). Handle exchange, in order of preference:
+//
+//   POSIX fd   cuMemCreate + cuMemExportToShareableHandle, fd passed between the rank
+//              processes with SCM_RIGHTS over abstract unix sockets whose names are
+//              published in the bootstrap store. Required for multicast.
+//   legacy IPC cudaMalloc + cudaIpcGetMemHandle through the store. P2P only.
+//   local      single process (world size 1, or the N-virtual-rank emulation).
+//
+// The CUDA driver API is reached through cudaGetDriverEntryPoint so the library has no
+// link-time dependency on libcuda.so.1 and still loads on a CPU-only box (where the
+// store and the argument checks remain usable and everything CUDA returns PDCC_ECUDA).
+//
+// Role parity: ProcessGroupNCCL construction / ncclCommInitRank / NVLS setup, reached
+// from the reference at main.py:94 and at every new_group (main.py:11,21,31,46,63,75).
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <errno.h>
+#include <string.h>
+#include <sys/socket.h>
+#include <sys/un.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "common.h"
+
+namespace pdcc {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+#define CUDA_TRY(expr)                                                              \
+  do {                                                                              \
+    cudaError_t e__ = (expr);                                                       \
+    if (e__ != cudaSuccess) {                                                       \
+      set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__,  \
+                __LINE__);                                                          \
+      return PDCC_ECUDA;                                                            \
+    }                                                                               \
+  } while (0)
+
+// ---------------------------------------------------------------- driver API table ---
+struct Driver {
+  bool ok = false;
+#define PDCC_DRV(name) decltype(&name) p_##name = nullptr;
+  PDCC_DRV(cuGetErrorString)
+  PDCC_DRV(cuDeviceGet)
+  PDCC_DRV(cuDeviceGetAttribute)
+  PDCC_DRV(cuMemGetAllocationGranularity)
+  PDCC_DRV(cuMemCreate)
+  PDCC_DRV(cuMemRelease)
+  PDCC_DRV(cuMemExportToShareableHandle)
+  PDCC_DRV(cuMemImportFromShareableHandle)
+  PDCC_DRV(cuMemAddressReserve)
+  PDCC_DRV(cuMemAddressFree)
+  PDCC_DRV(cuMemMap)
+  PDCC_DRV(cuMemUnmap)
+  PDCC_DRV(cuMemSetAccess)
+  PDCC_DRV(cuMulticastCreate)
+  PDCC_DRV(cuMulticastAddDevice)
+  PDCC_DRV(cuMulticastBindMem)
+  PDCC_DRV(cuMulticastGetGranularity)
+#undef PDCC_DRV
+};
+
+static Driver g_drv;
+static std::once_flag g_drv_once;
+
+static void load_driver() {
+  Driver d;
+  bool all = true;
+#define PDCC_LOAD(name)                                                                     \
+  do {                                                                                      \
+    void* fn = nullptr;                                                                     \
+    cudaDriverEntryPointQueryResult q;                                                      \
+    if (cudaGetDriverEntryPoint(#name, &fn, cudaEnableDefault, &q) != cudaSuccess || !fn)   \
+      all = false;                                                                          \
+    d.p_##name = reinterpret_cast<decltype(&name)>(fn);                                     \
+  } while (0)
+  PDCC_LOAD(cuGetErrorString);
+  PDCC_LOAD(cuDeviceGet);
+  PDCC_LOAD(cuDeviceGetAttribute);
+  PDCC_LOAD(cuMemGetAllocationGranularity);
+  PDCC_LOAD(cuMemCreate);
+  PDCC_LOAD(cuMemRelease);
+  PDCC_LOAD(cuMemExportToShareableHandle);
+  PDCC_LOAD(cuMemImportFromShareableHandle);
+  PDCC_LOAD(cuMemAddressReserve);
+  PDCC_LOAD(cuMemAddressFree);
+  PDCC_LOAD(cuMemMap);
+  PDCC_LOAD(cuMemUnmap);
+  PDCC_LOAD(cuMemSetAccess);
+  PDCC_LOAD(cuMulticastCreate);
+  PDCC_LOAD(cuMulticastAddDevice);
+  PDCC_LOAD(cuMulticastBindMem);
+  PDCC_LOAD(cuMulticastGetGranularity);
+#undef PDCC_LOAD
+  (void)cudaGetLastError();
+  d.ok = all;
+  g_drv = d;
+}
+
+static const Driver& drv() {
+  std::call_once(g_drv_once, load_driver);
+  return g_drv;
+}
+
+static const char* cu_err(CUresult r) {
+  const char* s = nullptr;
+  if (drv().p_cuGetErrorString && drv().p_cuGetErrorString(r, &s) == CUDA_SUCCESS && s) return s;
+  return "unknown CUresult";
+}
+
+#define CU_TRY(call)                                                                 \
+  do {                                                                               \
+    CUresult r__ = drv().p_##call;                                                   \
+    if (r__ != CUDA_SUCCESS) {                                                       \
+      set_error("%s failed: %s (%s:%d)", #call, cu_err(r__), __FILE__, __LINE__);    \
+      return PDCC_ECUDA;                                                             \
+    }                                                                                \
+  } while (0)
+
+static size_t round_up_sz(size_t v, size_t m) { return (v + m - 1) / m * m; }
+
+// ---------------------------------------------------------------- fd passing ---------
+// One message = {kind, src_rank} + one fd in the ancillary data.
+struct FdMsg {
+  int kind;  // 0: memory handle, 1: multicast handle
+  int src;
+};
+
+static int make_listener(const std::string& name) {
+  int fd = ::socket(AF_UNIX, SOCK_STREAM, 0);
+  if (fd < 0) return -1;
+  sockaddr_un addr{};
+  addr.sun_family = AF_UNIX;
+  // abstract namespace: leading NUL, no filesystem entry to clean up
+  memcpy(addr.sun_path + 1, name.data(), std::min(name.size(), sizeof(addr.sun_path) - 2));
+  socklen_t len = socklen_t(offsetof(sockaddr_un, sun_path) + 1 + name.size());
+  if (::bind(fd, reinterpret_cast<sockaddr*>(&addr), len) != 0 || ::listen(fd, 64) != 0) {
+    ::close(fd);
+    return -1;
+  }
+  return fd;
+}
+
+static int connect_to(const std::string& name, int timeout_ms) {
+  auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
+  for (;;) {
+    int fd = ::socket(AF_UNIX, SOCK_STREAM, 0);
+    if (fd < 0) return -1;
+    sockaddr_un addr{};
+    addr.sun_family = AF_UNIX;
+    memcpy(addr.sun_path + 1, name.data(), std::min(name.size(), sizeof(addr.sun_path) - 2));
+    socklen_t len = socklen_t(offsetof(sockaddr_un, sun_path) + 1 + name.size());
+    if (::connect(fd, reinterpret_cast<sockaddr*>(&addr), len) == 0) return fd;
+    ::close(fd);
+    if (std::chrono::steady_clock::now() > deadline) return -1;
+    std::this_thread::sleep_for(std::chrono::milliseconds(5));
+  }
+}
+
+static bool send_fd(int sock, const FdMsg& m, int fd) {
+  msghdr msg{};
+  iovec io{const_cast<FdMsg*>(&m), sizeof(m)};
+  msg.msg_iov = &io;
+  msg.msg_iovlen = 1;
+  char ctl[CMSG_SPACE(sizeof(int))];
+  memset(ctl, 0, sizeof(ctl));
+  msg.msg_control = ctl;
+  msg.msg_controllen = sizeof(ctl);
+  cmsghdr* c = CMSG_FIRSTHDR(&msg);
+  c->cmsg_level = SOL_SOCKET;
+  c->cmsg_type = SCM_RIGHTS;
+  c->cmsg_len = CMSG_LEN(sizeof(int));
+  memcpy(CMSG_DATA(c), &fd, sizeof(int));
+  return ::sendmsg(sock, &msg, MSG_NOSIGNAL) == ssize_t(sizeof(m));
+}
+
+static bool recv_fd(int sock, FdMsg* m, int* fd) {
+  msghdr msg{};
+  iovec io{m, sizeof(*m)};
+  msg.msg_iov = &io;
+  msg.msg_iovlen = 1;
+  char ctl[CMSG_SPACE(sizeof(int))];
+  memset(ctl, 0, sizeof(ctl));
+  msg.msg_control = ctl;
+  msg.msg_controllen = sizeof(ctl);
+  ssize_t k;
+  do {
+    k = ::recvmsg(sock, &msg, 0);
+  } while (k < 0 && errno == EINTR);
+  if (k != ssize_t(sizeof(*m))) return false;
+  cmsghdr* c = CMSG_FIRSTHDR(&msg);
+  if (!c || c->cmsg_level != SOL_SOCKET || c->cmsg_type != SCM_RIGHTS) return false;
+  memcpy(fd, CMSG_DATA(c), sizeof(int));
+  return true;
+}
+
+// Accept `count` messages on `lsock`; out[src] = fd for messages of `kind`.
+static bool accept_fds(int lsock, int count, int kind, std::vector<int>* out, int timeout_ms) {
+  auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
+  int got = 0;
+  while (got < count) {
+    timeval tv{0, 200000};
+    fd_set rs;
+    FD_ZERO(&rs);
+    FD_SET(lsock, &rs);
+    int r = ::select(lsock + 1, &rs, nullptr, nullptr, &tv);
+    if (r <= 0) {
+      if (std::chrono::steady_clock::now() > deadline) return false;
+      continue;
+    }
+    int s = ::accept(lsock, nullptr, nullptr);
+    if (s < 0) continue;
+    FdMsg m;
+    int fd = -1;
+    bool ok = recv_fd(s, &m, &fd);
+    ::close(s);
+    if (!ok) return false;
+    if (m.kind != kind || m.src < 0 || m.src >= int(out->size())) {
+      if (fd >= 0) ::close(fd);
+      return false;
+    }
+    (*out)[m.src] = fd;
+    ++got;
+  }
+  return true;
+}
+
+}  // namespace pdcc
+
+using namespace pdcc;
+
+// ---------------------------------------------------------------- comm object --------
+struct Mapping {
+  CUmemGenericAllocationHandle handle = 0;
+  CUdeviceptr va = 0;
+  size_t size = 0;
+  bool mapped = false;
+  bool have_handle = false;
+};
+
+struct pdcc_comm {
+  pdcc_comm_config_t cfg{};
+  int kind = PDCC_HANDLE_LOCAL;
+  int sm_count = 0;
+  int max_blocks = PDCC_MAX_BLOCKS;
+  size_t slot_bytes = 0;
+  size_t block_bytes = 0;
+  size_t heap_off = 0;
+  bool has_mc = false;
+  Mapping peers[PDCC_MAX_RANKS];  // POSIX-fd path
+  Mapping mc;
+  void* legacy_base = nullptr;  // cudaMalloc'd block (legacy IPC / local)
+  void* legacy_peer[PDCC_MAX_RANKS] = {};
+  DevComm dev{};
+};
+
+static void unmap(Mapping& m) {
+  const Driver& d = drv();
+  if (m.mapped) {
+    d.p_cuMemUnmap(m.va, m.size);
+    m.mapped = false;
+  }
+  if (m.va) {
+    d.p_cuMemAddressFree(m.va, m.size);
+    m.va = 0;
+  }
+  if (m.have_handle) {
+    d.p_cuMemRelease(m.handle);
+    m.have_handle = false;
+  }
+}
+
+static int map_handle(Mapping& m, size_t size, int device) {
+  m.size = size;
+  CU_TRY(cuMemAddressReserve(&m.va, size, 0, 0, 0));
+  CU_TRY(cuMemMap(m.va, size, 0, m.handle, 0));
+  m.mapped = true;
+  CUmemAccessDesc acc{};
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = device;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  CU_TRY(cuMemSetAccess(m.va, size, &acc, 1));
+  return PDCC_OK;
+}
+
+static std::string skey(const pdcc_comm_config_t& cfg, const char* what, int idx = -1) {
+  char buf[192];
+  if (idx >= 0) snprintf(buf, sizeof(buf), "%s/%s/%d", cfg.key, what, idx);
+  else snprintf(buf, sizeof(buf), "%s/%s", cfg.key, what);
+  return buf;
+}
+
+static int store_put_int(pdcc_store_t* st, const std::string& key, int v) {
+  return pdcc_store_set(st, key.c_str(), &v, sizeof(v));
+}
+static int store_get_int(pdcc_store_t* st, const std::string& key, int* v, int timeout_ms) {
+  int len = 0;
+  int rc = pdcc_store_get(st, key.c_str(), v, sizeof(*v), &len, timeout_ms);
+  if (rc == PDCC_OK && len != int(sizeof(*v))) {
+    set_error("store key %s has unexpected length %d", key.c_str(), len);
+    return PDCC_ESYS;
+  }
+  return rc;
+}
+
+extern "C" {
+
+const char* pdcc_last_error(void) { return g_err; }
+const char* pdcc_version(void) { return "pdcc 0.1 (sm_100a)"; }
+
+int pdcc_probe(int device, pdcc_caps_t* caps) {
+  if (!caps) return PDCC_EINVAL;
+  memset(caps, 0, sizeof(*caps));
+  caps->device = device;
+  int count = 0;
+  CUDA_TRY(cudaGetDeviceCount(&count));
+  caps->device_count = count;
+  if (device < 0 || device >= count) {
+    set_error("device %d out of range (%d devices)", device, count);
+    return PDCC_EINVAL;
+  }
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  snprintf(caps->name, sizeof(caps->name), "%s", prop.name);
+  caps->sm_count = prop.multiProcessorCount;
+  caps->cc_major = prop.major;
+  caps->cc_minor = prop.minor;
+  caps->total_mem = prop.totalGlobalMem;
+  caps->cooperative_launch = prop.cooperativeLaunch;
+  CUDA_TRY(cudaSetDevice(device));
+  CUDA_TRY(cudaFree(nullptr));
+  const Driver& d = drv();
+  if (!d.ok) return PDCC_OK;  // runtime-only box: everything else stays 0
+  CUdevice cudev;
+  CU_TRY(cuDeviceGet(&cudev, device));
+  int v = 0;
+  if (d.p_cuDeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_VIRTUAL_MEMORY_MANAGEMENT_SUPPORTED,
+                               cudev) == CUDA_SUCCESS)
+    caps->vmm_supported = v;
+  if (d.p_cuDeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR_SUPPORTED,
+                               cudev) == CUDA_SUCCESS)
+    caps->posix_fd_supported = v;
+  if (d.p_cuDeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_HANDLE_TYPE_FABRIC_SUPPORTED, cudev) ==
+      CUDA_SUCCESS)
+    caps->fabric_supported = v;
+  if (d.p_cuDeviceGetAttribute(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, cudev) == CUDA_SUCCESS)
+    caps->multicast_supported = v;
+  CUmemAllocationProp ap{};
+  ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ap.location.id = device;
+  ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  size_t g = 0;
+  if (caps->vmm_supported &&
+      d.p_cuMemGetAllocationGranularity(&g, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED) ==
+          CUDA_SUCCESS)
+    caps->alloc_granularity = g;
+  if (caps->multicast_supported && count >= 2) {
+    CUmulticastObjectProp mp{};
+    mp.numDevices = 2;
+    mp.size = 2 << 20;
+    mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    if (d.p_cuMulticastGetGranularity(&g, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) ==
+        CUDA_SUCCESS)
+      caps->mc_granularity = g;
+  }
+  return PDCC_OK;
+}
+
+static int fill_dev(pdcc_comm* c) {
+  c->dev.rank = c->cfg.rank;
+  c->dev.nranks = c->cfg.nranks;
+  c->dev.slot_bytes = uint32_t(c->slot_bytes);
+  c->dev.timeout_ms = uint32_t(c->cfg.device_timeout_ms > 0 ? c->cfg.device_timeout_ms : 10000);
+  for (int p = 0; p < PDCC_MAX_RANKS; ++p) c->dev.base[p] = nullptr;
+  for (int p = 0; p < c->cfg.nranks; ++p) {
+    if (c->kind == PDCC_HANDLE_POSIX_FD) c->dev.base[p] = reinterpret_cast<char*>(c->peers[p].va);
+    else c->dev.base[p] = static_cast<char*>(c->legacy_peer[p]);
+  }
+  c->dev.mc = c->has_mc ? reinterpret_cast<char*>(c->mc.va) : nullptr;
+  return PDCC_OK;
+}
+
+static void sizes_from_cfg(pdcc_comm* c) {
+  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(1) << 20);
+  c->max_blocks = c->cfg.max_blocks > 0 ? c->cfg.max_blocks : PDCC_MAX_BLOCKS;
+  if (c->max_blocks > PDCC_MAX_BLOCKS) c->max_blocks = PDCC_MAX_BLOCKS;
+  c->heap_off = kHeaderBytes + size_t(c->max_blocks) * PDCC_RING_DEPTH * c->slot_bytes;
+  c->block_bytes = c->heap_off + c->cfg.heap_bytes;
+}
+
+int pdcc_comm_destroy(pdcc_comm_t* c) {
+  if (!c) return PDCC_EINVAL;
+  cudaSetDevice(c->cfg.device);
+  cudaDeviceSynchronize();
+  if (c->kind == PDCC_HANDLE_POSIX_FD) {
+    unmap(c->mc);
+    for (int p = 0; p < c->cfg.nranks; ++p) unmap(c->peers[p]);
+  } else {
+    for (int p = 0; p < c->cfg.nranks; ++p)
+      if (p != c->cfg.rank && c->legacy_peer[p]) cudaIpcCloseMemHandle(c->legacy_peer[p]);
+    if (c->legacy_base) cudaFree(c->legacy_base);
+  }
+  delete c;
+  return PDCC_OK;
+}
+
+static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
+  const Driver& d = drv();
+  const pdcc_comm_config_t& cfg = c->cfg;
+  const int n = cfg.nranks, me = cfg.rank, tmo = cfg.timeout_ms;
+
+  CUmemAllocationProp ap{};
+  ap.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  ap.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  ap.location.id = cfg.device;
+  ap.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  size_t gran = 0;
+  CU_TRY(cuMemGetAllocationGranularity(&gran, &ap, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+  CUmulticastObjectProp mp{};
+  if (want_mc) {
+    mp.numDevices = unsigned(n);
+    mp.size = c->block_bytes;
+    mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+    size_t mg = 0;
+    if (d.p_cuMulticastGetGranularity(&mg, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) ==
+            CUDA_SUCCESS && mg > gran)
+      gran = mg;
+  }
+  c->block_bytes = round_up_sz(c->block_bytes, gran);
+  mp.size = c->block_bytes;
+
+  // my block
+  Mapping& mine = c->peers[me];
+  CU_TRY(cuMemCreate(&mine.handle, c->block_bytes, &ap, 0));
+  mine.have_handle = true;
+  int my_fd = -1;
+  CU_TRY(cuMemExportToShareableHandle(&my_fd, mine.handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR,
+                                      0));
+
+  // listener, published in the store
+  char sname[160];
+  snprintf(sname, sizeof(sname), "pdcc-%s-%d-%d", cfg.key, me, int(getpid()));
+  int lsock = make_listener(sname);
+  if (lsock < 0) {
+    set_error("cannot bind unix socket %s: %s", sname, strerror(errno));
+    ::close(my_fd);
+    return PDCC_ESYS;
+  }
+  int rc = pdcc_store_set(st, skey(cfg, "sock", me).c_str(), sname, int(strlen(sname)));
+  if (rc) return rc;
+
+  // receive in a helper thread while this thread sends
+  std::vector<int> fds(n, -1);
+  bool recv_ok = false;
+  std::thread rx([&] { recv_ok = accept_fds(lsock, n - 1, 0, &fds, tmo); });
+  bool send_ok = true;
+  std::string send_err;
+  for (int i = 1; i < n && send_ok; ++i) {
+    const int p = (me + i) % n;
+    char pname[160] = {0};
+    int len = 0;
+    rc = pdcc_store_get(st, skey(cfg, "sock", p).c_str(), pname, sizeof(pname) - 1, &len, tmo);
+    if (rc) {
+      send_ok = false;
+      break;
+    }
+    int s = connect_to(std::string(pname, size_t(len)), tmo);
+    if (s < 0 || !send_fd(s, FdMsg{0, me}, my_fd)) {
+      send_err = std::string("sending fd to rank ") + std::to_string(p) + ": " + strerror(errno);
+      send_ok = false;
+    }
+    if (s >= 0) ::close(s);
+  }
+  rx.join();
+  ::close(my_fd);
+  if (!send_ok || !recv_ok) {
+    set_error("fd exchange failed (%s%s)", send_ok ? "" : send_err.c_str(),
+              recv_ok ? "" : " receive timed out");
+    ::close(lsock);
+    return PDCC_ESYS;
+  }
+
+  // map every block (mine included) into this process
+  rc = map_handle(mine, c->block_bytes, cfg.device);
+  if (rc) return rc;
+  for (int p = 0; p < n; ++p) {
+    if (p == me) continue;
+    Mapping& m = c->peers[p];
+    CUresult r = d.p_cuMemImportFromShareableHandle(
+        &m.handle, reinterpret_cast<void*>(static_cast<uintptr_t>(fds[p])),
+        CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+    ::close(fds[p]);
+    if (r != CUDA_SUCCESS) {
+      set_error("cuMemImportFromShareableHandle(rank %d): %s", p, cu_err(r));
+      ::close(lsock);
+      return PDCC_ECUDA;
+    }
+    m.have_handle = true;
+    rc = map_handle(m, c->block_bytes, cfg.device);
+    if (rc) {
+      ::close(lsock);
+      return rc;
+    }
+  }
+
+  // Nobody may still be collecting memory handles when rank 0 starts handing out the
+  // multicast handle on the same sockets.
+  rc = pdcc_store_barrier(st, skey(cfg, "memx").c_str(), n, tmo);
+  if (rc) {
+    ::close(lsock);
+    return rc;
+  }
+
+  // ---- multicast: every step is voted on so that all ranks agree on has_mc ----------
+  c->has_mc = false;
+  if (want_mc) {
+    int ok = 1;
+    CUdevice cudev = 0;
+    if (d.p_cuDeviceGet(&cudev, cfg.device) != CUDA_SUCCESS) ok = 0;
+    if (me == 0) {
+      int mfd = -1;
+      if (ok && d.p_cuMulticastCreate(&c->mc.handle, &mp) != CUDA_SUCCESS) ok = 0;
+      if (ok) c->mc.have_handle = true;
+      if (ok && d.p_cuMemExportToShareableHandle(&mfd, c->mc.handle,
+                                                 CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR,
+                                                 0) != CUDA_SUCCESS)
+        ok = 0;
+      store_put_int(st, skey(cfg, "mc_created"), ok);
+      if (ok) {
+        for (int p = 1; p < n; ++p) {
+          char pname[160] = {0};
+          int len = 0;
+          if (pdcc_store_get(st, skey(cfg, "sock", p).c_str(), pname, sizeof(pname) - 1, &len,
+                             tmo))
+            continue;
+          int s = connect_to(std::string(pname, size_t(len)), tmo);
+          if (s >= 0) {
+            send_fd(s, FdMsg{1, 0}, mfd);
+            ::close(s);
+          }
+        }
+        ::close(mfd);
+      }
+    } else {
+      int created = 0;
+      if (store_get_int(st, skey(cfg, "mc_created"), &created, tmo) != PDCC_OK) created = 0;
+      if (!created) {
+        ok = 0;
+      } else {
+        std::vector<int> mfds(n, -1);
+        if (!accept_fds(lsock, 1, 1, &mfds, tmo)) {
+          ok = 0;
+        } else {
+          if (d.p_cuMemImportFromShareableHandle(
+                  &c->mc.handle, reinterpret_cast<void*>(static_cast<uintptr_t>(mfds[0])),
+                  CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR) != CUDA_SUCCESS)
+            ok = 0;
+          else
+            c->mc.have_handle = true;
+          ::close(mfds[0]);
+        }
+      }
+    }
+    if (ok && d.p_cuMulticastAddDevice(c->mc.handle, cudev) != CUDA_SUCCESS) ok = 0;
+    // vote 1: everyone added its device (binding before that is an error)
+    store_put_int(st, skey(cfg, "mc_add", me), ok);
+    for (int p = 0; p < n; ++p) {
+      int v = 0;
+      if (store_get_int(st, skey(cfg, "mc_add", p), &v, tmo) != PDCC_OK || !v) ok = 0;
+    }
+    if (ok && d.p_cuMulticastBindMem(c->mc.handle, 0, mine.handle, 0, c->block_bytes, 0) !=
+                  CUDA_SUCCESS)
+      ok = 0;
+    if (ok) {
+      c->mc.size = c->block_bytes;
+      if (d.p_cuMemAddressReserve(&c->mc.va, c->block_bytes, gran, 0, 0) != CUDA_SUCCESS) {
+        ok = 0;
+        c->mc.va = 0;
+      }
+    }
+    if (ok) {
+      if (d.p_cuMemMap(c->mc.va, c->block_bytes, 0, c->mc.handle, 0) != CUDA_SUCCESS) ok = 0;
+      else c->mc.mapped = true;
+    }
+    if (ok) {
+      CUmemAccessDesc acc{};
+      acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+      acc.location.id = cfg.device;
+      acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+      if (d.p_cuMemSetAccess(c->mc.va, c->block_bytes, &acc, 1) != CUDA_SUCCESS) ok = 0;
+    }
+    // vote 2: everyone bound and mapped
+    store_put_int(st, skey(cfg, "mc_bound", me), ok);
+    for (int p = 0; p < n; ++p) {
+      int v = 0;
+      if (store_get_int(st, skey(cfg, "mc_bound", p), &v, tmo) != PDCC_OK || !v) ok = 0;
+    }
+    c->has_mc = ok != 0;
+    if (!c->has_mc) unmap(c->mc);
+  }
+  ::close(lsock);
+  return PDCC_OK;
+}
+
+static int create_legacy(pdcc_comm* c, pdcc_store_t* st) {
+  const pdcc_comm_config_t& cfg = c->cfg;
+  const int n = cfg.nranks, me = cfg.rank, tmo = cfg.timeout_ms;
+  CUDA_TRY(cudaMalloc(&c->legacy_base, c->block_bytes));
+  c->legacy_peer[me] = c->legacy_base;
+  if (n == 1) return PDCC_OK;
+  cudaIpcMemHandle_t h;
+  CUDA_TRY(cudaIpcGetMemHandle(&h, c->legacy_base));
+  int rc = pdcc_store_set(st, skey(cfg, "ipc", me).c_str(), &h, sizeof(h));
+  if (rc) return rc;
+  for (int p = 0; p < n; ++p) {
+    if (p == me) continue;
+    cudaIpcMemHandle_t ph;
+    int len = 0;
+    rc = pdcc_store_get(st, skey(cfg, "ipc", p).c_str(), &ph, sizeof(ph), &len, tmo);
+    if (rc) return rc;
+    CUDA_TRY(cudaIpcOpenMemHandle(&c->legacy_peer[p], ph, cudaIpcMemLazyEnablePeerAccess));
+  }
+  return PDCC_OK;
+}
+
+int pdcc_comm_create(pdcc_store_t* st, const pdcc_comm_config_t* cfg_in, pdcc_comm_t** out) {
+  if (!cfg_in || !out) return PDCC_EINVAL;
+  pdcc_comm_config_t cfg = *cfg_in;
+  if (cfg.nranks < 1 || cfg.nranks > PDCC_MAX_RANKS || cfg.rank < 0 || cfg.rank >= cfg.nranks) {
+    set_error("bad rank/nranks %d/%d (max %d ranks)", cfg.rank, cfg.nranks, PDCC_MAX_RANKS);
+    return PDCC_EINVAL;
+  }
+  if (cfg.nranks > 1 && !st) {
+    set_error("a store is required for nranks > 1");
+    return PDCC_EINVAL;
+  }
+  if (cfg.timeout_ms <= 0) cfg.timeout_ms = 120000;
+  cfg.key[sizeof(cfg.key) - 1] = 0;
+
+  pdcc_caps_t caps;
+  int rc = pdcc_probe(cfg.device, &caps);
+  if (rc) return rc;
+
+  auto* c = new pdcc_comm();
+  c->cfg = cfg;
+  c->sm_count = caps.sm_count;
+  sizes_from_cfg(c);
+
+  const int n = cfg.nranks, me = cfg.rank;
+  if (n == 1) {
+    c->kind = PDCC_HANDLE_LOCAL;
+    rc = create_legacy(c, st);
+  } else {
+    // agree on the handle kind: everyone publishes what it can do
+    int mine[2] = {caps.vmm_supported && caps.posix_fd_supported && drv().ok,
+                   caps.multicast_supported};
+    if (cfg.handle_kind == PDCC_HANDLE_LEGACY_IPC) mine[0] = 0;
+    if (cfg.multicast == 0) mine[1] = 0;
+    rc = pdcc_store_set(st, skey(cfg, "caps", me).c_str(), mine, sizeof(mine));
+    bool all_posix = true, all_mc = true;
+    for (int p = 0; p < n && rc == PDCC_OK; ++p) {
+      int theirs[2] = {0, 0};
+      int len = 0;
+      rc = pdcc_store_get(st, skey(cfg, "caps", p).c_str(), theirs, sizeof(theirs), &len,
+                          cfg.timeout_ms);
+      all_posix = all_posix && theirs[0];
+      all_mc = all_mc && theirs[1];
+    }
+    if (rc == PDCC_OK) {
+      if (all_posix) {
+        c->kind = PDCC_HANDLE_POSIX_FD;
+        rc = create_posix(c, st, all_mc);
+      } else if (cfg.handle_kind == PDCC_HANDLE_POSIX_FD) {
+        set_error("POSIX fd handles requested but not supported on every rank");
+        rc = PDCC_EUNSUPPORTED;
+      } else {
+        c->kind = PDCC_HANDLE_LEGACY_IPC;
+        rc = create_legacy(c, st);
+      }
+    }
+    if (rc == PDCC_OK && cfg.multicast == 1 && !c->has_mc) {
+      set_error("multicast required but could not be set up on every rank");
+      rc = PDCC_EUNSUPPORTED;
+    }
+  }
+  if (rc != PDCC_OK) {
+    std::string keep = g_err;
+    pdcc_comm_destroy(c);
+    set_error("%s", keep.c_str());
+    return rc;
+  }
+  fill_dev(c);
+
+  // zero ctrl + pads of my block, then make sure nobody signals into a block that has
+  // not been zeroed yet
+  cudaError_t e = cudaMemset(c->dev.base[me], 0, kHeaderBytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    set_error("zeroing the block header: %s", cudaGetErrorString(e));
+    pdcc_comm_destroy(c);
+    return PDCC_ECUDA;
+  }
+  if (n > 1) {
+    rc = pdcc_store_barrier(st, skey(cfg, "ready").c_str(), n, cfg.timeout_ms);
+    if (rc) {
+      pdcc_comm_destroy(c);
+      return rc;
+    }
+  }
+  *out = c;
+  return PDCC_OK;
+}
+
+int pdcc_comm_info(pdcc_comm_t* c, pdcc_comm_info_t* info) {
+  if (!c || !info) return PDCC_EINVAL;
+  memset(info, 0, sizeof(*info));
+  info->rank = c->cfg.rank;
+  info->nranks = c->cfg.nranks;
+  info->device = c->cfg.device;
+  info->handle_kind = c->kind;
+  info->has_multicast = c->has_mc;
+  info->sm_count = c->sm_count;
+  info->max_blocks = c->max_blocks;
+  info->slot_bytes = c->slot_bytes;
+  info->block_bytes = c->block_bytes;
+  info->heap_bytes = c->cfg.heap_bytes;
+  info->heap_base = c->cfg.heap_bytes ? c->dev.base[c->cfg.rank] + c->heap_off : nullptr;
+  return PDCC_OK;
+}
+
+static int check_block(char* base, int rank) {
+  uint32_t err[2] = {0, 0};
+  CUDA_TRY(cudaMemcpy(err, base, sizeof(err), cudaMemcpyDeviceToHost));
+  if (err[0] != 0) {
+    const uint32_t info = err[1];
+    set_error("rank %d: device-side wait timed out (channel %u, waiting on rank %u, flag value "
+              "0x%06x): peers are not running the same collective sequence",
+              rank, info >> 28, (info >> 24) & 0xfu, info & 0xffffffu);
+    uint32_t zero[2] = {0, 0};
+    cudaMemcpy(base, zero, sizeof(zero), cudaMemcpyHostToDevice);
+    return PDCC_EPEER;
+  }
+  return PDCC_OK;
+}
+
+int pdcc_comm_check(pdcc_comm_t* c) {
+  if (!c) return PDCC_EINVAL;
+  CUDA_TRY(cudaSetDevice(c->cfg.device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  return check_block(c->dev.base[c->cfg.rank], c->cfg.rank);
+}
+
+static int ring_limit(const pdcc_comm* c) {
+  return c->max_blocks < c->sm_count || c->sm_count <= 0 ? c->max_blocks : c->sm_count;
+}
+
+int pdcc_plan(pdcc_comm_t* c, const pdcc_op_t* op, int* algo, int* nblocks, int* threads,
+              uint64_t* tile_bytes, int* ntiles) {
+  if (!c || !op) return PDCC_EINVAL;
+  Plan p;
+  int rc = plan_collective(c->dev, ring_limit(c), c->has_mc, *op, &p);
+  if (rc) return rc;
+  if (algo) *algo = p.algo;
+  if (nblocks) *nblocks = p.nblocks;
+  if (threads) *threads = p.threads;
+  if (tile_bytes) *tile_bytes = p.tile_bytes;
+  if (ntiles) *ntiles = p.ntiles;
+  return PDCC_OK;
+}
+
+static int validate_ptrs(const pdcc_op_t& op, int rank, int n) {
+  if (op.count == 0 || op.coll == PDCC_BARRIER) return PDCC_OK;
+  auto need = [&](const void* p, const char* what) {
+    if (!p) {
+      set_error("collective %d: %s pointer is null on rank %d", op.coll, what, rank);
+      return false;
+    }
+    return true;
+  };
+  switch (op.coll) {
+    case PDCC_ALL_REDUCE:
+      if (!need(op.in, "in") || !need(op.out, "out")) return PDCC_EINVAL;
+      break;
+    case PDCC_REDUCE:
+      if (!need(op.in, "in")) return PDCC_EINVAL;
+      if (rank == op.root && !need(op.out, "out")) return PDCC_EINVAL;
+      break;
+    case PDCC_BROADCAST:
+      if (rank == op.root ? !need(op.in, "in") : !need(op.out, "out")) return PDCC_EINVAL;
+      break;
+    case PDCC_SCATTER:
+      if (!need(op.out, "out")) return PDCC_EINVAL;
+      if (rank == op.root)
+        for (int j = 0; j < n; ++j)
+          if (!need(op.list[j], "scatter_list[j]")) return PDCC_EINVAL;
+      break;
+    case PDCC_GATHER:
+      if (!need(op.in, "in")) return PDCC_EINVAL;
+      if (rank == op.root)
+        for (int j = 0; j < n; ++j)
+          if (!need(op.list[j], "gather_list[j]")) return PDCC_EINVAL;
+      break;
+    case PDCC_ALL_GATHER:
+      if (!need(op.in, "in")) return PDCC_EINVAL;
+      for (int j = 0; j < n; ++j)
+        if (!need(op.list[j], "tensor_list[j]")) return PDCC_EINVAL;
+      break;
+    default:
+      break;
+  }
+  return PDCC_OK;
+}
+
+static void fill_rank_args(RankArgs* ra, const DevComm& dev, const pdcc_op_t& op) {
+  ra->comm = dev;
+  ra->in = op.in;
+  ra->out = op.out;
+  for (int j = 0; j < PDCC_MAX_RANKS; ++j) ra->list[j] = op.list[j];
+}
+
+int pdcc_collective(pdcc_comm_t* c, const pdcc_op_t* op_in, void* stream) {
+  if (!c || !op_in) return PDCC_EINVAL;
+  pdcc_op_t op = *op_in;
+  if (op.coll != PDCC_ALL_REDUCE) op.out_dtype = op.dtype;
+  if (op.count == 0 && op.coll != PDCC_BARRIER) return PDCC_OK;
+  int rc = validate_ptrs(op, c->cfg.rank, c->cfg.nranks);
+  if (rc) return rc;
+  Plan p;
+  rc = plan_collective(c->dev, ring_limit(c), c->has_mc, op, &p);
+  if (rc) return rc;
+  RankArgs ra;
+  fill_rank_args(&ra, c->dev, op);
+  return launch_collective(&ra, 1, nullptr, op, p, stream);
+}
+
+static pdcc_op_t base_op(int coll, uint64_t count, int dtype) {
+  pdcc_op_t op;
+  memset(&op, 0, sizeof(op));
+  op.coll = coll;
+  op.count = count;
+  op.dtype = dtype;
+  op.out_dtype = dtype;
+  op.redop = PDCC_SUM;
+  op.scale = 1.0f;
+  return op;
+}
+
+int pdcc_all_reduce(pdcc_comm_t* c, void* buf, uint64_t count, int dtype, int redop,
+                    void* stream) {
+  pdcc_op_t op = base_op(PDCC_ALL_REDUCE, count, dtype);
+  op.in = buf;
+  op.out = buf;
+  op.redop = redop;
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_all_reduce_scaled(pdcc_comm_t* c, const void* in, void* out, uint64_t count, int dtype,
+                           int out_dtype, float scale, void* stream) {
+  pdcc_op_t op = base_op(PDCC_ALL_REDUCE, count, dtype);
+  op.in = in;
+  op.out = out;
+  op.out_dtype = out_dtype;
+  op.scale = scale;
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_reduce(pdcc_comm_t* c, void* buf, uint64_t count, int dtype, int redop, int dst,
+                void* stream) {
+  pdcc_op_t op = base_op(PDCC_REDUCE, count, dtype);
+  op.in = buf;
+  op.out = buf;
+  op.redop = redop;
+  op.root = dst;
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_broadcast(pdcc_comm_t* c, void* buf, uint64_t count, int dtype, int src, void* stream) {
+  pdcc_op_t op = base_op(PDCC_BROADCAST, count, dtype);
+  op.in = buf;
+  op.out = buf;
+  op.root = src;
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_scatter(pdcc_comm_t* c, void* out, void* const* scatter_list, uint64_t count, int dtype,
+                 int src, void* stream) {
+  if (!c) return PDCC_EINVAL;
+  pdcc_op_t op = base_op(PDCC_SCATTER, count, dtype);
+  op.out = out;
+  op.root = src;
+  if (scatter_list)
+    for (int j = 0; j < c->cfg.nranks; ++j) op.list[j] = scatter_list[j];
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_gather(pdcc_comm_t* c, const void* in, void* const* gather_list, uint64_t count,
+                int dtype, int dst, void* stream) {
+  if (!c) return PDCC_EINVAL;
+  pdcc_op_t op = base_op(PDCC_GATHER, count, dtype);
+  op.in = in;
+  op.root = dst;
+  if (gather_list)
+    for (int j = 0; j < c->cfg.nranks; ++j) op.list[j] = gather_list[j];
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_all_gather(pdcc_comm_t* c, void* const* out_list, const void* in, uint64_t count,
+                    int dtype, void* stream) {
+  if (!c || !out_list) return PDCC_EINVAL;
+  pdcc_op_t op = base_op(PDCC_ALL_GATHER, count, dtype);
+  op.in = in;
+  for (int j = 0; j < c->cfg.nranks; ++j) op.list[j] = out_list[j];
+  return pdcc_collective(c, &op, stream);
+}
+
+int pdcc_barrier(pdcc_comm_t* c, void* stream) {
+  pdcc_op_t op = base_op(PDCC_BARRIER, 0, PDCC_U8);
+  return pdcc_collective(c, &op, stream);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------- emulation ----------
+struct pdcc_emu {
+  int device = 0;
+  int nranks = 0;
+  int sm_count = 0;
+  int max_blocks = 0;
+  size_t slot_bytes = 0;
+  size_t block_bytes = 0;
+  char* blocks[PDCC_MAX_RANKS] = {};
+  RankArgs* dev_args = nullptr;
+  DevComm dev[PDCC_MAX_RANKS];
+};
+
+extern "C" {
+
+int pdcc_emu_destroy(pdcc_emu_t* e) {
+  if (!e) return PDCC_EINVAL;
+  cudaSetDevice(e->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < e->nranks; ++r)
+    if (e->blocks[r]) cudaFree(e->blocks[r]);
+  if (e->dev_args) cudaFree(e->dev_args);
+  delete e;
+  return PDCC_OK;
+}
+
+int pdcc_emu_create(int device, int nranks, size_t slot_bytes, int max_blocks,
+                    int device_timeout_ms, pdcc_emu_t** out) {
+  if (!out || nranks < 1 || nranks > PDCC_MAX_RANKS) {
+    set_error("emu: nranks must be 1..%d", PDCC_MAX_RANKS);
+    return PDCC_EINVAL;
+  }
+  pdcc_caps_t caps;
+  int rc = pdcc_probe(device, &caps);
+  if (rc) return rc;
+  if (!caps.cooperative_launch) {
+    set_error("emu: device %d has no cooperative launch", device);
+    return PDCC_EUNSUPPORTED;
+  }
+  auto* e = new pdcc_emu();
+  e->device = device;
+  e->nranks = nranks;
+  e->sm_count = caps.sm_count;
+  e->slot_bytes = slot_bytes ? round_up_sz(slot_bytes, 4096) : (size_t(256) << 10);
+  e->max_blocks = max_blocks > 0 ? max_blocks : 16;
+  if (e->max_blocks > PDCC_MAX_BLOCKS) e->max_blocks = PDCC_MAX_BLOCKS;
+  // every emulated rank's CTAs must be resident at once
+  if (e->max_blocks * nranks > caps.sm_count) e->max_blocks = caps.sm_count / nranks;
+  e->block_bytes = kHeaderBytes + size_t(e->max_blocks) * PDCC_RING_DEPTH * e->slot_bytes;
+  for (int r = 0; r < nranks; ++r) {
+    cudaError_t ce = cudaMalloc(reinterpret_cast<void**>(&e->blocks[r]), e->block_bytes);
+    if (ce == cudaSuccess) ce = cudaMemset(e->blocks[r], 0, kHeaderBytes);
+    if (ce != cudaSuccess) {
+      set_error("emu: allocating block %d: %s", r, cudaGetErrorString(ce));
+      pdcc_emu_destroy(e);
+      return PDCC_ECUDA;
+    }
+  }
+  if (cudaMalloc(reinterpret_cast<void**>(&e->dev_args), sizeof(RankArgs) * PDCC_MAX_RANKS) !=
+      cudaSuccess) {
+    set_error("emu: allocating args");
+    pdcc_emu_destroy(e);
+    return PDCC_ECUDA;
+  }
+  for (int r = 0; r < nranks; ++r) {
+    DevComm& d = e->dev[r];
+    memset(&d, 0, sizeof(d));
+    d.rank = r;
+    d.nranks = nranks;
+    for (int p = 0; p < nranks; ++p) d.base[p] = e->blocks[p];
+    d.mc = nullptr;
+    d.slot_bytes = uint32_t(e->slot_bytes);
+    d.timeout_ms = uint32_t(device_timeout_ms > 0 ? device_timeout_ms : 5000);
+  }
+  cudaDeviceSynchronize();
+  *out = e;
+  return PDCC_OK;
+}
+
+int pdcc_emu_collective(pdcc_emu_t* e, const pdcc_op_t* ops, void* stream) {
+  if (!e || !ops) return PDCC_EINVAL;
+  CUDA_TRY(cudaSetDevice(e->device));
+  pdcc_op_t op0 = ops[0];
+  if (op0.coll != PDCC_ALL_REDUCE) op0.out_dtype = op0.dtype;
+  if (op0.count == 0 && op0.coll != PDCC_BARRIER) return PDCC_OK;
+  RankArgs host[PDCC_MAX_RANKS];
+  for (int r = 0; r < e->nranks; ++r) {
+    const pdcc_op_t& o = ops[r];
+    if (o.coll != op0.coll || o.count != op0.count || o.dtype != op0.dtype ||
+        o.redop != op0.redop || o.root != op0.root || o.algo != op0.algo ||
+        o.nblocks != op0.nblocks) {
+      set_error("emu: rank %d describes a different collective than rank 0", r);
+      return PDCC_EINVAL;
+    }
+    int rc = validate_ptrs(o, r, e->nranks);
+    if (rc) return rc;
+    fill_rank_args(&host[r], e->dev[r], o);
+  }
+  Plan p;
+  const int limit = e->max_blocks;
+  int rc = plan_collective(e->dev[0], limit, false, op0, &p);
+  if (rc) return rc;
+  if (e->nranks == 1) return launch_collective(host, 1, nullptr, op0, p, stream);
+  // pageable source: the copy is staged before this returns, so `host` may die
+  CUDA_TRY(cudaMemcpyAsync(e->dev_args, host, sizeof(RankArgs) * e->nranks,
+                           cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  return launch_collective(host, e->nranks, e->dev_args, op0, p, stream);
+}
+
+int pdcc_emu_check(pdcc_emu_t* e) {
+  if (!e) return PDCC_EINVAL;
+  CUDA_TRY(cudaSetDevice(e->device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  for (int r = 0; r < e->nranks; ++r) {
+    int rc = check_block(e->blocks[r], r);
+    if (rc) return rc;
+  }
+  return PDCC_OK;
+}
+
+}  // extern "C"
