@@ -128,3 +128,132 @@ def crash_rank1(rank, size):
     if rank == 1:
         raise SystemExit(3)
     dist.barrier()
+
+
+def _det_input(rank, count, dtype, seed, dev):
+    g = torch.Generator(device="cpu").manual_seed(1000 * seed + rank)
+    if dtype.is_floating_point:
+        x = torch.rand(count, generator=g, dtype=torch.float64) * 2 - 1
+    else:
+        x = torch.randint(-3, 4, (count,), generator=g).double()
+    return x.to(dtype).to(dev)
+
+
+def native_sweep(rank, size):
+    """Every collective x dtype x op x size x algorithm variant on real GPUs, against an
+    oracle each rank rebuilds locally from the seeds."""
+    from pdcc_b200.ops import collectives as K
+
+    dev = demos.device()
+    world = dist.new_group(list(range(size)))
+    comm = dist.native_comm(world)
+    failures, checked = [], 0
+    sizes = [1, 5, 1024, 4099, 262144 + 3, 3 * (1 << 20) + 1]
+    ar_algos = ["oneshot_p2p", "twoshot_p2p"]
+    if comm.has_multicast:
+        ar_algos += ["oneshot_nvls", "twoshot_nvls"]
+    ops = {"SUM": K.SUM, "PRODUCT": K.PRODUCT, "MIN": K.MIN, "MAX": K.MAX}
+
+    def oracle(count, dtype, seed, op):
+        st = torch.stack([_det_input(r, count, dtype, seed, "cpu").double() for r in range(size)])
+        return {"SUM": st.sum(0), "PRODUCT": st.prod(0), "MIN": st.min(0).values,
+                "MAX": st.max(0).values}[op]
+
+    seed = 0
+    for dtype in (torch.float32, torch.bfloat16, torch.float16, torch.int32):
+        for opname, op in ops.items():
+            for algo in ar_algos:
+                if "nvls" in algo and (opname == "PRODUCT" or
+                                       (dtype == torch.float32 and opname != "SUM")):
+                    continue
+                for count in sizes:
+                    seed += 1
+                    x = _det_input(rank, count, dtype, seed, dev)
+                    comm.all_reduce(x, op, algo=algo)
+                    want = oracle(count, dtype, seed, opname)
+                    tol = 0.0
+                    if dtype.is_floating_point and opname in ("SUM", "PRODUCT"):
+                        tol = {torch.float32: 1e-5, torch.bfloat16: 4e-2, torch.float16: 5e-3}[dtype]
+                    got = x.cpu().double()
+                    checked += 1
+                    if not torch.allclose(got, want, rtol=tol, atol=tol):
+                        failures.append(("all_reduce", str(dtype), opname, algo, count,
+                                         float((got - want).abs().max())))
+    rooted_algos = ["p2p"] + (["nvls"] if comm.has_multicast else [])
+    for count in sizes:
+        for root in (0, size - 1):
+            for algo in rooted_algos:
+                seed += 1
+                x = _det_input(rank, count, torch.float32, seed, dev)
+                keep = x.clone()
+                comm.reduce(x, root, K.SUM, algo=algo)
+                checked += 1
+                if rank == root:
+                    if not torch.allclose(x.cpu().double(), oracle(count, torch.float32, seed, "SUM"),
+                                          rtol=1e-5, atol=1e-5):
+                        failures.append(("reduce", algo, count, root))
+                elif not torch.equal(x, keep):
+                    failures.append(("reduce-nonroot-touched", algo, count, root))
+                seed += 1
+                x = _det_input(rank, count, torch.float32, seed, dev)
+                comm.broadcast(x, root, algo=algo)
+                checked += 1
+                if not torch.equal(x.cpu(), _det_input(root, count, torch.float32, seed, "cpu")):
+                    failures.append(("broadcast", algo, count, root))
+                seed += 1
+                x = _det_input(rank, count, torch.bfloat16, seed, dev)
+                lst = [torch.zeros(count, dtype=torch.bfloat16, device=dev) for _ in range(size)]
+                comm.all_gather(lst, x, algo=algo)
+                checked += 1
+                for p in range(size):
+                    if not torch.equal(lst[p].cpu(), _det_input(p, count, torch.bfloat16, seed, "cpu")):
+                        failures.append(("all_gather", algo, count, p))
+                        break
+            seed += 1
+            out = torch.zeros(count, device=dev)
+            sl = [_det_input(100 + j, count, torch.float32, seed, dev) for j in range(size)] \
+                if rank == root else None
+            comm.scatter(out, sl, root)
+            checked += 1
+            if not torch.equal(out.cpu(), _det_input(100 + rank, count, torch.float32, seed, "cpu")):
+                failures.append(("scatter", count, root))
+            seed += 1
+            x = _det_input(rank, count, torch.float32, seed, dev)
+            gl = [torch.zeros(count, device=dev) for _ in range(size)] if rank == root else None
+            comm.gather(x, gl, root)
+            checked += 1
+            if rank == root:
+                for p in range(size):
+                    if not torch.equal(gl[p].cpu(), _det_input(p, count, torch.float32, seed, "cpu")):
+                        failures.append(("gather", count, root, p))
+                        break
+    # stress: no host sync between 300 mixed calls
+    xs = []
+    for it in range(300):
+        count = sizes[it % 4]
+        x = _det_input(rank, count, torch.float32, 5000 + it, dev)
+        if it % 3 == 0:
+            comm.all_reduce(x, K.SUM)
+        elif it % 3 == 1:
+            comm.broadcast(x, it % size)
+        else:
+            comm.reduce(x, it % size, K.MAX)
+        xs.append((it, count, x))
+    for it, count, x in xs:
+        checked += 1
+        if it % 3 == 0:
+            ok = torch.allclose(x.cpu().double(), oracle(count, torch.float32, 5000 + it, "SUM"),
+                                rtol=1e-5, atol=1e-5)
+        elif it % 3 == 1:
+            ok = torch.equal(x.cpu(), _det_input(it % size, count, torch.float32, 5000 + it, "cpu"))
+        else:
+            ok = rank != it % size or torch.equal(
+                x.cpu().double(), oracle(count, torch.float32, 5000 + it, "MAX"))
+        if not ok:
+            failures.append(("stress", it, count))
+    try:
+        comm.check()
+    except Exception as e:  # device-side timeout
+        failures.append(("device", str(e)))
+    _save(rank, "sweep", {"failures": failures, "checked": checked,
+                          "multicast": comm.has_multicast, "handle": comm.handle_kind})

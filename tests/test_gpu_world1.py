@@ -1,0 +1,77 @@
+"""Single-GPU degenerate case: world size 1 on the native backend, where
+every collective is a copy or a no-op, plus the local K9 kernels."""
+import os
+
+import pytest
+import torch
+
+import pdcc_b200 as dist
+from pdcc_b200 import _native as N
+from pdcc_b200.ops import collectives as K
+import _workers
+
+pytestmark = pytest.mark.gpu
+
+
+def test_probe_reports_b200_capabilities():
+    caps = N.probe(0)
+    assert caps["sm_count"] > 0 and caps["cooperative_launch"] == 1
+    print(caps)
+
+
+def test_local_copy_and_scale_cast():
+    for nbytes in (1, 15, 16, 4097, 1 << 20, (1 << 24) + 3):
+        src = torch.randint(0, 255, (nbytes,), dtype=torch.uint8, device="cuda")
+        dst = torch.zeros_like(src)
+        K.local_copy(dst, src)
+        assert torch.equal(dst, src)
+    off = torch.randint(0, 255, (5000,), dtype=torch.uint8, device="cuda")
+    d2 = torch.zeros(5001, dtype=torch.uint8, device="cuda")
+    K.local_copy(d2[1:], off)
+    assert torch.equal(d2[1:], off)
+    x = torch.randn(100003, device="cuda").bfloat16()
+    o32 = torch.empty(100003, device="cuda")
+    K.local_scale_cast(o32, x, 0.25)
+    torch.testing.assert_close(o32, x.float() * 0.25, rtol=1e-6, atol=1e-6)
+    o16 = torch.empty_like(x)
+    K.local_scale_cast(o16, x, 0.5)
+    torch.testing.assert_close(o16.float(), x.float() * 0.5, rtol=1e-2, atol=1e-2)
+
+
+def test_world1_native_comm_runs_every_kernel():
+    """nranks == 1 through the real communicator object (self-signalling flags)."""
+    comm = K.NativeComm(None, "w1", 0, 1, 0, slot_bytes=64 << 10, max_blocks=8)
+    assert comm.handle_kind == "local" and not comm.has_multicast
+    before = N.launch_count()
+    x = torch.randn(100001, device="cuda")
+    ref = x.clone()
+    comm.all_reduce(x, K.SUM, algo="oneshot_p2p")
+    comm.all_reduce(x, K.MAX, algo="twoshot_p2p")
+    comm.reduce(x, 0, K.SUM)
+    comm.broadcast(x, 0)
+    out = torch.zeros_like(x)
+    comm.scatter(out, [x], 0)
+    lst = [torch.zeros_like(x)]
+    comm.gather(x, lst, 0)
+    lst2 = [torch.zeros_like(x)]
+    comm.all_gather(lst2, x)
+    comm.barrier()
+    comm.check()
+    assert N.launch_count() - before == 8
+    for t in (x, out, lst[0], lst2[0]):
+        assert torch.equal(t, ref)
+    comm.destroy()
+
+
+@pytest.mark.parametrize("name", ["do_reduce", "do_all_reduce", "do_scatter", "do_gather",
+                                  "do_all_gather", "do_broadcast", "hello_world"])
+def test_demos_world1_b200(name, tmp_path):
+    """The reference's demos with size=1 on cuda:0 through init_process(..., 'b200')."""
+    dist.launch(_workers.run_demo, size=1, backend="b200", timeout=300,
+                env={"PDCC_TEST_OUT": str(tmp_path), "PDCC_TEST_DEMO": name})
+    res = torch.load(os.path.join(tmp_path, f"{name}_0.pt"))
+    want = {"do_reduce": 1.0, "do_all_reduce": 1.0, "do_scatter": 1.0, "do_broadcast": 0.0}
+    if name in want:
+        assert res.item() == want[name]
+    elif name in ("do_gather", "do_all_gather"):
+        assert [t.item() for t in res] == [0.0]
