@@ -17,7 +17,8 @@ void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
 //
 //   [0, kCtrlBytes)                 ctrl   local-only bookkeeping (epochs, error record)
 //   [kCtrlBytes, kHeaderBytes)      pads   signal flags written by peers
-//   [kHeaderBytes, +rings)          rings  max_blocks x PDCC_RING_DEPTH tile slots
+//   [kHeaderBytes, +kLLBytes)       LL     kLLRings x PDCC_RING_DEPTH flag-in-data slots
+//   [kDataOffset, +rings)           rings  max_blocks x PDCC_RING_DEPTH tile slots
 //   [.., +heap_bytes)               heap   symmetric heap for zero-copy user tensors
 //
 // Every CTA index b owns ring b on every rank: slot(b, pos) sits at the same offset in
@@ -30,6 +31,14 @@ constexpr size_t kPadBytes =
     size_t(kNumChannels) * PDCC_MAX_BLOCKS * PDCC_MAX_RANKS * sizeof(uint32_t);
 constexpr size_t kHeaderBytes = 2 * 1024 * 1024;  // keeps rings 2 MiB aligned
 static_assert(kCtrlBytes + kPadBytes <= kHeaderBytes, "header too small");
+// LL (low-latency) slots hold {data, flag, data, flag} packets only, never raw payload, so
+// a stale word can never be mistaken for the current flag. They stay zero-initialised
+// until first use and are only used by the first kLLRings CTA indices.
+constexpr int kLLRings = 16;
+constexpr size_t kLLSlotBytes = 256 * 1024;
+constexpr size_t kLLBytes = size_t(kLLRings) * PDCC_RING_DEPTH * kLLSlotBytes;  // 16 MiB
+constexpr size_t kDataOffset = kHeaderBytes + kLLBytes;
+constexpr size_t kZeroBytes = kDataOffset;  // what comm creation must clear
 
 // ctrl words (uint32 index)
 constexpr int kCtrlErr = 0;        // first device-side timeout record: code

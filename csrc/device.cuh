@@ -157,8 +157,11 @@ struct Ctx {
   int* poisoned;      // smem: a wait already timed out in this CTA
 
   __device__ __forceinline__ size_t slot_off(uint32_t g) const {
-    return kHeaderBytes +
+    return kDataOffset +
            (size_t(b) * PDCC_RING_DEPTH + (g % PDCC_RING_DEPTH)) * a->comm.slot_bytes;
+  }
+  __device__ __forceinline__ size_t ll_off(uint32_t g) const {
+    return kHeaderBytes + (size_t(b) * PDCC_RING_DEPTH + (g % PDCC_RING_DEPTH)) * kLLSlotBytes;
   }
   __device__ __forceinline__ char* peer(int p, size_t off) const { return a->comm.base[p] + off; }
   __device__ __forceinline__ char* mine(size_t off) const { return a->comm.base[rank] + off; }
@@ -181,10 +184,29 @@ __device__ __forceinline__ void signal(const Ctx& c, int chan, uint32_t val, uin
   }
 }
 
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// DONE(g) publishes no data: it only says "I no longer touch ring position g % DEPTH", and
+// every access it covers has already returned its value to this CTA (a load whose result
+// was consumed) or is ordered behind it per address. A relaxed store after bar.sync is
+// enough and keeps a system fence off the tail of every tile.
+__device__ __forceinline__ void signal_relaxed(const Ctx& c, int chan, uint32_t val,
+                                               uint32_t mask) {
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < c.n && ((mask >> t) & 1u)) {
+    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
+    st_relaxed_sys(pad + flag_index(chan, c.b, c.rank), val);
+  }
+}
+
 // All threads call. Thread t waits for rank t's flag to reach val (wrap-safe), then a
 // system-scope fence makes it an acquire; bar.sync hands the guarantee to the whole CTA.
 // A wait that outlives the budget records an error and poisons the CTA instead of
 // hanging the GPU.
+template <bool ACQUIRE = true>
 __device__ __forceinline__ void wait(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
   const int t = threadIdx.x;
   if (t < c.n && ((mask >> t) & 1u) && !*c.poisoned) {
@@ -198,7 +220,9 @@ __device__ __forceinline__ void wait(const Ctx& c, int chan, uint32_t val, uint3
         break;
       }
     }
-    fence_acq_rel_sys();
+    // The slot guard (ACQUIRE = false) only orders this CTA's later *writes* after the
+    // peers' completed reads; the control dependency on the flag does that without a fence.
+    if constexpr (ACQUIRE) fence_acq_rel_sys();
   }
   __syncthreads();
 }

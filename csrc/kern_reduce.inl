@@ -1,7 +1,7 @@
 // Included by kern_<dtype>.cu with PDCC_T (element type), PDCC_NAME (table function) and
 // PDCC_HAS_WIDE (16-bit floats: also build the fp32-output variant) defined. One
 // translation unit per dtype keeps the nvcc jobs parallel.
-#include "kernels.cuh"
+#include "ll.cuh"
 
 namespace pdcc {
 
@@ -13,6 +13,7 @@ PDCC_DECLARE_REDUCE_TABLE(PDCC_NAME) {
     case AR_TWOSHOT_P2P:  return R ? nullptr : reduce_kernel<T, W, AR_TWOSHOT_P2P, false>;  \
     case AR_ONESHOT_NVLS: return reduce_kernel<T, W, AR_ONESHOT_NVLS, R>;    \
     case AR_TWOSHOT_NVLS: return R ? nullptr : reduce_kernel<T, W, AR_TWOSHOT_NVLS, false>; \
+    case AR_LL:           return ll_reduce_kernel<T, W, R>;                  \
     default: return nullptr;                                                 \
   }
 #if PDCC_HAS_WIDE

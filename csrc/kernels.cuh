@@ -48,43 +48,51 @@ struct Geo {
   }
 };
 
-template <class P>
-__device__ __forceinline__ void run_pipeline(const KArgs& k) {
-  __shared__ uint32_t s_g0;
-  __shared__ int s_poison;
-  __shared__ RankArgs s_args;  // emulation only: this virtual rank's args
+// Shared kernel prologue: pick this (virtual) rank's args, read the ring's tile counter.
+struct Prologue {
+  uint32_t g0;
+  int poison;
+  RankArgs args;  // emulation only: this virtual rank's args
+};
 
+__device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
   const RankArgs* a = &k.r;
   if (k.emu != nullptr) {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(k.emu + blockIdx.y);
-    uint32_t* dst = reinterpret_cast<uint32_t*>(&s_args);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&sh.args);
     for (int i = threadIdx.x; i < int(sizeof(RankArgs) / 4); i += blockDim.x) dst[i] = src[i];
     __syncthreads();
-    a = &s_args;
+    a = &sh.args;
   }
-
-  Ctx c;
   c.a = a;
   c.rank = a->comm.rank;
   c.n = a->comm.nranks;
   c.b = blockIdx.x;
   c.my_pad = reinterpret_cast<uint32_t*>(a->comm.base[c.rank] + kCtrlBytes);
   c.ctrl = reinterpret_cast<uint32_t*>(a->comm.base[c.rank]);
-  c.poisoned = &s_poison;
+  c.poisoned = &sh.poison;
   c.deadline = globaltimer_ns() + uint64_t(a->comm.timeout_ms) * 1000000ull;
   if (threadIdx.x == 0) {
-    s_g0 = c.ctrl[kCtrlEpoch + c.b];
-    s_poison = 0;
+    sh.g0 = c.ctrl[kCtrlEpoch + c.b];
+    sh.poison = 0;
   }
   __syncthreads();
-  c.g0 = s_g0;
+  c.g0 = sh.g0;
+}
+
+template <class P>
+__device__ __forceinline__ void run_pipeline(const KArgs& k) {
+  __shared__ Prologue sh;
+  Ctx c;
+  init_ctx(k, sh, c);
 
   const uint32_t all = (1u << c.n) - 1u;
   const int T = k.ntiles;
   P p(k, c);
 
-  // ring position of tile g is free once every rank finished tile g - DEPTH
-  auto guard = [&](uint32_t g) { wait(c, CH_DONE, g - PDCC_RING_DEPTH + 1u, all); };
+  // Ring position of tile g is free once every rank finished tile g - DEPTH. Flags start
+  // at 0 and the compare is wrap-safe, so the first DEPTH tiles pass immediately.
+  auto guard = [&](uint32_t g) { wait<false>(c, CH_DONE, g - PDCC_RING_DEPTH + 1u, all); };
 
   guard(c.g0);
   p.in(0);
@@ -103,16 +111,16 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
       if (t >= 1) {
         wait(c, CH_MID, g, all);
         p.out(t - 1);
-        signal(c, CH_DONE, g, all);
+        signal_relaxed(c, CH_DONE, g, all);
       }
     } else {
-      signal(c, CH_DONE, g + 1u, all);
+      signal_relaxed(c, CH_DONE, g + 1u, all);
     }
   }
   if constexpr (P::kHasOut) {
     wait(c, CH_MID, c.g0 + uint32_t(T), all);
     p.out(T - 1);
-    signal(c, CH_DONE, c.g0 + uint32_t(T), all);
+    signal_relaxed(c, CH_DONE, c.g0 + uint32_t(T), all);
   }
   if (threadIdx.x == 0) c.ctrl[kCtrlEpoch + c.b] = c.g0 + uint32_t(T);
 }
@@ -120,7 +128,7 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
 // ---------------------------------------------------------------------------------------
 // K1/K2/K3: all_reduce (main.py:23), fused scale+cast (README.md:5), reduce (main.py:14)
 // ---------------------------------------------------------------------------------------
-enum ArAlgo : int { AR_ONESHOT_P2P, AR_TWOSHOT_P2P, AR_ONESHOT_NVLS, AR_TWOSHOT_NVLS };
+enum ArAlgo : int { AR_ONESHOT_P2P, AR_TWOSHOT_P2P, AR_ONESHOT_NVLS, AR_TWOSHOT_NVLS, AR_LL };
 
 template <typename T, bool WIDE, int OP, int ALGO, bool ROOTED>
 struct ReducePolicy {
@@ -150,16 +158,99 @@ struct ReducePolicy {
                            len);
   }
 
-  // combine unit j of the slot over all peers in rank order
-  __device__ __forceinline__ void gather_units(size_t so, size_t j, Acc<T>& acc) const {
-    uint4 v[PDCC_MAX_RANKS];
+  // P2P: U units per thread per pass, every peer's 16-byte load issued before the first
+  // combine, so U x n loads are in flight per thread (NVLink round trips are ~2 us: one
+  // load in flight per thread would cap a GPU at ~150 GB/s). Peers are combined in rank
+  // order 0..n-1 on every rank => bitwise identical results.
+  template <int NP, int U, bool TWOSHOT>
+  __device__ __forceinline__ void mid_p2p(size_t so, size_t lo, size_t hi, size_t nelem,
+                                          size_t elem0) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const bool scaled = k.scale != 1.0f;
+    for (size_t j0 = lo + tid; j0 < hi; j0 += size_t(nt) * U) {
+      uint4 v[U][NP];
 #pragma unroll
-    for (int p = 0; p < PDCC_MAX_RANKS; ++p)
-      if (p < c.n) v[p] = ld_sys_v4(c.peer(p, so) + (j << 4));
-    acc.init(v[0]);
+      for (int u = 0; u < U; ++u) {
+        const size_t j = j0 + size_t(u) * nt;
+        if (j < hi) {
 #pragma unroll
-    for (int p = 1; p < PDCC_MAX_RANKS; ++p)
-      if (p < c.n) acc.template add<OP>(v[p]);
+          for (int p = 0; p < NP; ++p)
+            if (p < c.n) v[u][p] = ld_sys_v4(c.peer(p, so) + (j << 4));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const size_t j = j0 + size_t(u) * nt;
+        if (j < hi) {
+          Acc<T> acc;
+          acc.init(v[u][0]);
+#pragma unroll
+          for (int p = 1; p < NP; ++p)
+            if (p < c.n) acc.template add<OP>(v[u][p]);
+          if (scaled) acc.scale(k.scale);
+          if constexpr (TWOSHOT) {
+            const uint4 res = acc.pack();
+#pragma unroll
+            for (int p = 0; p < NP; ++p)
+              if (p < c.n) st_v4(c.peer(p, so) + (j << 4), res);
+          } else {
+            const size_t e = j * Tr::K;
+            const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
+            store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
+          }
+        }
+      }
+    }
+  }
+
+  template <bool TWOSHOT>
+  __device__ __forceinline__ void mid_p2p_dispatch(size_t so, size_t lo, size_t hi, size_t nelem,
+                                                   size_t elem0) {
+    if (c.n <= 2) mid_p2p<2, 8, TWOSHOT>(so, lo, hi, nelem, elem0);
+    else if (c.n <= 4) mid_p2p<4, 4, TWOSHOT>(so, lo, hi, nelem, elem0);
+    else mid_p2p<8, 2, TWOSHOT>(so, lo, hi, nelem, elem0);
+  }
+
+  // NVLS: the switch reduces; 8 multimem.ld_reduce in flight per thread.
+  template <bool TWOSHOT>
+  __device__ __forceinline__ void mid_nvls(size_t so, size_t lo, size_t hi, size_t nelem,
+                                           size_t elem0) {
+    if constexpr (kMm != MM_NONE) {
+      constexpr int U = 8;
+      const int tid = threadIdx.x, nt = blockDim.x;
+      const bool scaled = k.scale != 1.0f;
+      for (size_t j0 = lo + tid; j0 < hi; j0 += size_t(nt) * U) {
+        uint4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const size_t j = j0 + size_t(u) * nt;
+          if (j < hi) v[u] = multimem_ld_reduce_v4<kMm>(c.mc(so) + (j << 4));
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const size_t j = j0 + size_t(u) * nt;
+          if (j < hi) {
+            if constexpr (TWOSHOT) {
+              uint4 r = v[u];
+              if (scaled) {
+                Acc<T> acc;
+                acc.init(r);
+                acc.scale(k.scale);
+                r = acc.pack();
+              }
+              multimem_st_v4(c.mc(so) + (j << 4), r);
+            } else {
+              Acc<T> acc;
+              acc.init(v[u]);
+              if (scaled) acc.scale(k.scale);
+              const size_t e = j * Tr::K;
+              const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
+              store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
+            }
+          }
+        }
+      }
+    }
   }
 
   __device__ __forceinline__ void mid(int t) {
@@ -168,50 +259,22 @@ struct ReducePolicy {
     geo.range(t, off, len);
     if (len == 0) return;
     const size_t so = c.slot_off(c.g0 + t);
-    const int tid = threadIdx.x, nt = blockDim.x;
     const size_t n16 = (len + 15) >> 4;
     const size_t nelem = len / sizeof(T);
     const size_t elem0 = off / sizeof(T);
-    const bool scaled = k.scale != 1.0f;
-
-    if constexpr (ALGO == AR_ONESHOT_P2P || ALGO == AR_ONESHOT_NVLS) {
-      for (size_t j = tid; j < n16; j += nt) {
-        Acc<T> acc;
-        if constexpr (ALGO == AR_ONESHOT_P2P) {
-          gather_units(so, j, acc);
-        } else if constexpr (kMm != MM_NONE) {
-          acc.init(multimem_ld_reduce_v4<kMm>(c.mc(so) + (j << 4)));
-        }
-        if (scaled) acc.scale(k.scale);
-        const size_t e = j * Tr::K;
-        const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
-        store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
-      }
+    if constexpr (ALGO == AR_ONESHOT_P2P) {
+      mid_p2p_dispatch<false>(so, 0, n16, nelem, elem0);
+    } else if constexpr (ALGO == AR_ONESHOT_NVLS) {
+      mid_nvls<false>(so, 0, n16, nelem, elem0);
     } else {
       // two-shot: this rank owns units [lo, hi) of the tile
       const size_t sub16 = (k.tile_bytes / c.n) >> 4;
       const size_t lo = size_t(c.rank) * sub16;
       size_t hi = lo + sub16;
       if (hi > n16) hi = n16;
-      for (size_t j = lo + tid; j < hi; j += nt) {
-        if constexpr (ALGO == AR_TWOSHOT_P2P) {
-          Acc<T> acc;
-          gather_units(so, j, acc);
-          if (scaled) acc.scale(k.scale);
-          const uint4 res = acc.pack();
-#pragma unroll
-          for (int p = 0; p < PDCC_MAX_RANKS; ++p)
-            if (p < c.n) st_v4(c.peer(p, so) + (j << 4), res);
-        } else if constexpr (kMm != MM_NONE) {
-          uint4 v = multimem_ld_reduce_v4<kMm>(c.mc(so) + (j << 4));
-          if (scaled) {
-            Acc<T> acc;
-            acc.init(v);
-            acc.scale(k.scale);
-            v = acc.pack();
-          }
-          multimem_st_v4(c.mc(so) + (j << 4), v);
-        }
+      if (lo < hi) {
+        if constexpr (ALGO == AR_TWOSHOT_P2P) mid_p2p_dispatch<true>(so, lo, hi, nelem, elem0);
+        else mid_nvls<true>(so, lo, hi, nelem, elem0);
       }
     }
   }

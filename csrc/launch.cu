@@ -8,7 +8,7 @@
 
 #include <atomic>
 
-#include "kernels.cuh"
+#include "ll.cuh"
 
 namespace pdcc {
 
@@ -60,6 +60,16 @@ static KernelFn move_kernel_for(int kind) {
   }
 }
 
+static KernelFn ll_move_kernel_for(int coll) {
+  switch (coll) {
+    case PDCC_BROADCAST: return ll_move_kernel<LL_BROADCAST>;
+    case PDCC_SCATTER: return ll_move_kernel<LL_SCATTER>;
+    case PDCC_GATHER: return ll_move_kernel<LL_GATHER>;
+    case PDCC_ALL_GATHER: return ll_move_kernel<LL_ALL_GATHER>;
+    default: return nullptr;
+  }
+}
+
 static uint64_t round_up(uint64_t v, uint64_t m) { return (v + m - 1) / m * m; }
 static uint64_t ceil_div(uint64_t a, uint64_t b) { return (a + b - 1) / b; }
 __device__ __forceinline__ uint64_t round_up_dev(uint64_t v, uint64_t m) { return (v + m - 1) / m * m; }
@@ -94,6 +104,26 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   // ---- algorithm -----------------------------------------------------------------
   int algo = op.algo;
   const bool mc_ok = has_mc && comm.mc != nullptr;
+  // Small messages: flag-in-data push (ll.cuh). Above the threshold the doubled wire
+  // bytes cost more than the fences they save. Thresholds from profiles/ sweeps.
+  if (algo == PDCC_ALGO_AUTO && op.coll != PDCC_BARRIER && n > 1 &&
+      bytes <= uint64_t(env_int("PDCC_LL_MAX", 32 << 10)))
+    algo = PDCC_ALGO_LL;
+  if (algo == PDCC_ALGO_LL) {
+    if (op.coll == PDCC_BARRIER) {
+      set_error("barrier has no LL variant");
+      return PDCC_EINVAL;
+    }
+    int nb = op.nblocks > 0 ? op.nblocks : int(ceil_div(bytes ? bytes : 1, kLLTileBytes));
+    int limit = ring_limit > 0 && ring_limit < kLLRings ? ring_limit : kLLRings;
+    if (nb > limit) nb = limit;
+    plan->algo = algo;
+    plan->nblocks = nb;
+    plan->threads = kThreads;
+    plan->tile_bytes = kLLTileBytes;
+    plan->ntiles = int(ceil_div(bytes ? bytes : 1, uint64_t(kLLTileBytes) * nb));
+    return PDCC_OK;
+  }
   if (op.coll == PDCC_ALL_REDUCE) {
     const bool nvls = mc_ok && nvls_reducible(op.dtype, redop);
     if (algo == PDCC_ALGO_AUTO) {
@@ -101,8 +131,12 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       // moves ~2 x bytes and needs two. Crossover measured on 8xB200 (profiles/).
       const uint64_t oneshot_max = nvls ? uint64_t(env_int("PDCC_ONESHOT_NVLS_MAX", 64 << 10))
                                         : uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10));
-      if (nvls) algo = bytes <= oneshot_max ? PDCC_ALGO_ONESHOT_NVLS : PDCC_ALGO_TWOSHOT_NVLS;
-      else algo = (bytes <= oneshot_max || n == 1) ? PDCC_ALGO_ONESHOT_P2P : PDCC_ALGO_TWOSHOT_P2P;
+      // Link bytes per GPU and direction: NVLS two-shot S(1 + 1/n) (the switch reads all of
+      // my data once, I receive my shard and everyone's broadcast), P2P two-shot
+      // 2S(n-1)/n. The switch wins from n = 4 up.
+      if (nvls && n >= 4) algo = bytes <= oneshot_max ? PDCC_ALGO_ONESHOT_NVLS : PDCC_ALGO_TWOSHOT_NVLS;
+      else algo = (bytes <= uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10)) || n == 1)
+                      ? PDCC_ALGO_ONESHOT_P2P : PDCC_ALGO_TWOSHOT_P2P;
     }
     if ((algo == PDCC_ALGO_ONESHOT_NVLS || algo == PDCC_ALGO_TWOSHOT_NVLS) && !nvls) {
       set_error("NVLS all_reduce not available for dtype %d op %d (multicast %s)", op.dtype,
@@ -237,7 +271,9 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
         set_error("fused cast supports bf16/f16 -> f32 only");
         return PDCC_EINVAL;
       }
-      fn = reduce_kernel_for(op.dtype, wide, plan.algo - PDCC_ALGO_ONESHOT_P2P, false);
+      fn = reduce_kernel_for(op.dtype, wide,
+                             plan.algo == PDCC_ALGO_LL ? AR_LL : plan.algo - PDCC_ALGO_ONESHOT_P2P,
+                             false);
       break;
     }
     case PDCC_REDUCE:
@@ -246,15 +282,24 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
         return PDCC_EINVAL;
       }
       fn = reduce_kernel_for(op.dtype, false,
-                             plan.algo == PDCC_ALGO_NVLS ? AR_ONESHOT_NVLS : AR_ONESHOT_P2P, true);
+                             plan.algo == PDCC_ALGO_LL     ? AR_LL
+                             : plan.algo == PDCC_ALGO_NVLS ? AR_ONESHOT_NVLS
+                                                           : AR_ONESHOT_P2P,
+                             true);
       break;
     case PDCC_BROADCAST:
-      fn = move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_BROADCAST_NVLS : MV_BROADCAST_P2P);
+      fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll)
+           : move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_BROADCAST_NVLS : MV_BROADCAST_P2P);
       break;
-    case PDCC_SCATTER: fn = move_kernel_for(MV_SCATTER); break;
-    case PDCC_GATHER: fn = move_kernel_for(MV_GATHER); break;
+    case PDCC_SCATTER:
+      fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll) : move_kernel_for(MV_SCATTER);
+      break;
+    case PDCC_GATHER:
+      fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll) : move_kernel_for(MV_GATHER);
+      break;
     case PDCC_ALL_GATHER:
-      fn = move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_ALLGATHER_NVLS : MV_ALLGATHER_PULL);
+      fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll)
+           : move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_ALLGATHER_NVLS : MV_ALLGATHER_PULL);
       break;
     case PDCC_BARRIER: fn = move_kernel_for(MV_BARRIER); break;
     default: break;

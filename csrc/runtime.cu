@@ -404,7 +404,7 @@ static void sizes_from_cfg(pdcc_comm* c) {
   c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(1) << 20);
   c->max_blocks = c->cfg.max_blocks > 0 ? c->cfg.max_blocks : PDCC_MAX_BLOCKS;
   if (c->max_blocks > PDCC_MAX_BLOCKS) c->max_blocks = PDCC_MAX_BLOCKS;
-  c->heap_off = kHeaderBytes + size_t(c->max_blocks) * PDCC_RING_DEPTH * c->slot_bytes;
+  c->heap_off = kDataOffset + size_t(c->max_blocks) * PDCC_RING_DEPTH * c->slot_bytes;
   c->block_bytes = c->heap_off + c->cfg.heap_bytes;
 }
 
@@ -711,9 +711,9 @@ int pdcc_comm_create(pdcc_store_t* st, const pdcc_comm_config_t* cfg_in, pdcc_co
   }
   fill_dev(c);
 
-  // zero ctrl + pads of my block, then make sure nobody signals into a block that has
+  // zero ctrl + pads + LL slots of my block, then make sure nobody signals into a block that has
   // not been zeroed yet
-  cudaError_t e = cudaMemset(c->dev.base[me], 0, kHeaderBytes);
+  cudaError_t e = cudaMemset(c->dev.base[me], 0, kZeroBytes);
   if (e == cudaSuccess) e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     set_error("zeroing the block header: %s", cudaGetErrorString(e));
@@ -988,10 +988,10 @@ int pdcc_emu_create(int device, int nranks, size_t slot_bytes, int max_blocks,
   if (e->max_blocks > PDCC_MAX_BLOCKS) e->max_blocks = PDCC_MAX_BLOCKS;
   // every emulated rank's CTAs must be resident at once
   if (e->max_blocks * nranks > caps.sm_count) e->max_blocks = caps.sm_count / nranks;
-  e->block_bytes = kHeaderBytes + size_t(e->max_blocks) * PDCC_RING_DEPTH * e->slot_bytes;
+  e->block_bytes = kDataOffset + size_t(e->max_blocks) * PDCC_RING_DEPTH * e->slot_bytes;
   for (int r = 0; r < nranks; ++r) {
     cudaError_t ce = cudaMalloc(reinterpret_cast<void**>(&e->blocks[r]), e->block_bytes);
-    if (ce == cudaSuccess) ce = cudaMemset(e->blocks[r], 0, kHeaderBytes);
+    if (ce == cudaSuccess) ce = cudaMemset(e->blocks[r], 0, kZeroBytes);
     if (ce != cudaSuccess) {
       set_error("emu: allocating block %d: %s", r, cudaGetErrorString(ce));
       pdcc_emu_destroy(e);

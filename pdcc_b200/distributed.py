@@ -410,11 +410,9 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op: bool = False):
         return None
     op = _redop(op)
     if tensor.is_cuda:
-        if tensor.numel() and g.size() > 1:
-            native_comm(g).all_reduce(tensor, int(op))
-        elif op == ReduceOp.AVG:
-            pass  # mean over one rank
-        return _finish(async_op, True)
+        if g.size() > 1 and tensor.numel():
+            (g.comm or native_comm(g)).all_reduce(tensor, int(op))
+        return _finish(async_op, True) if async_op else None
     if op == ReduceOp.AVG:  # gloo has no AVG: sum then divide
         work = tdist.all_reduce(tensor, op=tdist.ReduceOp.SUM, group=g.torch_pg, async_op=False)
         tensor.div_(g.size())

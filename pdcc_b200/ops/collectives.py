@@ -46,8 +46,15 @@ def _algo(algo) -> int:
     return int(algo)
 
 
-def _stream_ptr(stream: Optional[torch.cuda.Stream]) -> int:
-    return (stream or torch.cuda.current_stream()).cuda_stream
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
+def _stream_ptr(stream: Optional[torch.cuda.Stream], device: int = -1) -> int:
+    if stream is not None:
+        return stream.cuda_stream
+    if _raw_stream is not None and device >= 0:
+        return _raw_stream(device)  # no Stream object on the hot path
+    return torch.cuda.current_stream().cuda_stream
 
 
 def _fill(op: N.Op, coll: int, count: int, dtype: int, *, out_dtype: Optional[int] = None,
@@ -64,9 +71,11 @@ def _fill(op: N.Op, coll: int, count: int, dtype: int, *, out_dtype: Optional[in
     op.count = count
     op.in_ = in_ptr
     op.out = out_ptr
-    lst = op.list
-    for j in range(N.MAX_RANKS):
-        lst[j] = ptrs[j] if j < len(ptrs) else None
+    if ptrs or getattr(op, "_has_list", True):
+        lst = op.list
+        for j in range(N.MAX_RANKS):
+            lst[j] = ptrs[j] if j < len(ptrs) else None
+        op._has_list = bool(ptrs)
     return op
 
 
@@ -98,12 +107,15 @@ class NativeComm:
         self.slot_bytes, self.block_bytes = info.slot_bytes, info.block_bytes
         self.heap_base, self.heap_bytes = info.heap_base, info.heap_bytes
         self._op = N.Op()  # reused: no per-call allocation on the hot path
+        self._op_ref = C.byref(self._op)
+        self._dev = torch.device("cuda", self.device)
         self._collective = L.pdcc_collective
         self._launches = 0
 
     # -- plumbing ---------------------------------------------------------------------
     def _run(self, op: N.Op, stream: Optional[torch.cuda.Stream]) -> None:
-        rc = self._collective(self._h, C.byref(op), _stream_ptr(stream))
+        rc = self._collective(self._h, self._op_ref if op is self._op else C.byref(op),
+                              _stream_ptr(stream, self.device))
         if rc != 0:
             N.check(rc)
 
@@ -129,7 +141,7 @@ class NativeComm:
             self._h = C.c_void_p()
 
     def _own(self, t: torch.Tensor) -> None:
-        if not t.is_cuda or t.device.index != self.device:
+        if t.device != self._dev:
             raise ValueError(f"tensor on {t.device} but this group's communicator is bound to "
                              f"cuda:{self.device}")
         if not t.is_contiguous():
@@ -169,7 +181,7 @@ class NativeComm:
         self._run(op, stream)
 
     def scatter(self, tensor: torch.Tensor, scatter_list: Optional[Sequence[torch.Tensor]], src: int,
-                *, nblocks: int = 0, stream=None) -> None:
+                *, algo=None, nblocks: int = 0, stream=None) -> None:
         """K5. `scatter_list` (one tensor per group rank) only on `src`."""
         self._own(tensor)
         ptrs: Sequence[int] = ()
@@ -178,12 +190,12 @@ class NativeComm:
                 self._own(t)
             ptrs = [t.data_ptr() for t in scatter_list]
         nbytes = tensor.numel() * tensor.element_size()
-        op = _fill(self._op, N.SCATTER, nbytes, N.U8, root=src, nblocks=nblocks,
+        op = _fill(self._op, N.SCATTER, nbytes, N.U8, root=src, algo=algo, nblocks=nblocks,
                    out_ptr=tensor.data_ptr(), ptrs=ptrs)
         self._run(op, stream)
 
     def gather(self, tensor: torch.Tensor, gather_list: Optional[Sequence[torch.Tensor]], dst: int,
-               *, nblocks: int = 0, stream=None) -> None:
+               *, algo=None, nblocks: int = 0, stream=None) -> None:
         """K6. `gather_list` only on `dst`."""
         self._own(tensor)
         ptrs: Sequence[int] = ()
@@ -192,7 +204,7 @@ class NativeComm:
                 self._own(t)
             ptrs = [t.data_ptr() for t in gather_list]
         nbytes = tensor.numel() * tensor.element_size()
-        op = _fill(self._op, N.GATHER, nbytes, N.U8, root=dst, nblocks=nblocks,
+        op = _fill(self._op, N.GATHER, nbytes, N.U8, root=dst, algo=algo, nblocks=nblocks,
                    in_ptr=tensor.data_ptr(), ptrs=ptrs)
         self._run(op, stream)
 
@@ -261,36 +273,36 @@ class Emulator:
                   scale=scale, in_ptr=t.data_ptr(), out_ptr=o.data_ptr())
         self._run()
 
-    def reduce(self, tensors, dst, redop=SUM, *, nblocks=0):
+    def reduce(self, tensors, dst, redop=SUM, *, algo=None, nblocks=0):
         for r, t in enumerate(tensors):
             _fill(self._ops[r], N.REDUCE, t.numel(), dtype_code(t.dtype, True), redop=redop,
-                  root=dst, nblocks=nblocks, in_ptr=t.data_ptr(), out_ptr=t.data_ptr())
+                  root=dst, algo=algo, nblocks=nblocks, in_ptr=t.data_ptr(), out_ptr=t.data_ptr())
         self._run()
 
-    def broadcast(self, tensors, src, *, nblocks=0):
+    def broadcast(self, tensors, src, *, algo=None, nblocks=0):
         for r, t in enumerate(tensors):
             _fill(self._ops[r], N.BROADCAST, t.numel() * t.element_size(), N.U8, root=src,
-                  nblocks=nblocks, in_ptr=t.data_ptr(), out_ptr=t.data_ptr())
+                  algo=algo, nblocks=nblocks, in_ptr=t.data_ptr(), out_ptr=t.data_ptr())
         self._run()
 
-    def scatter(self, outs, scatter_list, src, *, nblocks=0):
+    def scatter(self, outs, scatter_list, src, *, algo=None, nblocks=0):
         for r, t in enumerate(outs):
             ptrs = [x.data_ptr() for x in scatter_list] if r == src else ()
             _fill(self._ops[r], N.SCATTER, t.numel() * t.element_size(), N.U8, root=src,
-                  nblocks=nblocks, out_ptr=t.data_ptr(), ptrs=ptrs)
+                  algo=algo, nblocks=nblocks, out_ptr=t.data_ptr(), ptrs=ptrs)
         self._run()
 
-    def gather(self, ins, gather_list, dst, *, nblocks=0):
+    def gather(self, ins, gather_list, dst, *, algo=None, nblocks=0):
         for r, t in enumerate(ins):
             ptrs = [x.data_ptr() for x in gather_list] if r == dst else ()
             _fill(self._ops[r], N.GATHER, t.numel() * t.element_size(), N.U8, root=dst,
-                  nblocks=nblocks, in_ptr=t.data_ptr(), ptrs=ptrs)
+                  algo=algo, nblocks=nblocks, in_ptr=t.data_ptr(), ptrs=ptrs)
         self._run()
 
-    def all_gather(self, out_lists, ins, *, nblocks=0):
+    def all_gather(self, out_lists, ins, *, algo=None, nblocks=0):
         for r, t in enumerate(ins):
-            _fill(self._ops[r], N.ALL_GATHER, t.numel() * t.element_size(), N.U8, nblocks=nblocks,
-                  in_ptr=t.data_ptr(), ptrs=[x.data_ptr() for x in out_lists[r]])
+            _fill(self._ops[r], N.ALL_GATHER, t.numel() * t.element_size(), N.U8, algo=algo,
+                  nblocks=nblocks, in_ptr=t.data_ptr(), ptrs=[x.data_ptr() for x in out_lists[r]])
         self._run()
 
     def barrier(self):

@@ -251,6 +251,30 @@ def native_sweep(rank, size):
                 x.cpu().double(), oracle(count, torch.float32, 5000 + it, "MAX"))
         if not ok:
             failures.append(("stress", it, count))
+    # CUDA-graph replay of a mixed sequence (LL + tile-pipelined + rooted)
+    small = torch.zeros(1000, device=dev)
+    big = torch.zeros(400003, device=dev)
+    comm.all_reduce(small, K.SUM)
+    comm.all_reduce(big, K.SUM)
+    comm.broadcast(big, size - 1)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            comm.all_reduce(small, K.SUM)
+            comm.all_reduce(big, K.SUM)
+            comm.broadcast(small, size - 1)
+    for i in range(1, 5):
+        small.fill_(float(rank + i))
+        big.fill_(float(i))
+        graph.replay()
+        torch.cuda.synchronize()
+        checked += 1
+        want_small = float(sum(r + i for r in range(size)))
+        if float(small[0]) != want_small or float(small[-1]) != want_small or \
+                float(big[0]) != float(i * size) or float(big[-1]) != float(i * size):
+            failures.append(("graph", i, float(small[0]), float(big[-1])))
     try:
         comm.check()
     except Exception as e:  # device-side timeout

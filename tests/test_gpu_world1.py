@@ -63,6 +63,33 @@ def test_world1_native_comm_runs_every_kernel():
     comm.destroy()
 
 
+def test_cuda_graph_replay_world1():
+    """Launches carry no host-side epoch (ring counters live on the device), so a captured
+    sequence of collectives can be replayed any number of times."""
+    comm = K.NativeComm(None, "w1g", 0, 1, 0, slot_bytes=64 << 10, max_blocks=8)
+    x = torch.zeros(300001, device="cuda")
+    y = torch.zeros(1000, device="cuda")
+    out, out2 = [torch.zeros_like(x)], torch.zeros_like(y)
+    comm.all_gather(out, x)
+    comm.scatter(out2, [y], 0)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(g, stream=side):
+            comm.all_gather(out, x)     # multi-tile, wraps the ring
+            comm.scatter(out2, [y], 0)
+            comm.all_reduce(y, K.SUM)
+    for i in range(1, 6):
+        x.fill_(float(i))
+        y.fill_(float(-i))
+        g.replay()
+        torch.cuda.synchronize()
+        assert float(out[0][0]) == i and float(out[0][-1]) == i and float(out2[7]) == -i
+    comm.check()
+    comm.destroy()
+
+
 @pytest.mark.parametrize("name", ["do_reduce", "do_all_reduce", "do_scatter", "do_gather",
                                   "do_all_gather", "do_broadcast", "hello_world"])
 def test_demos_world1_b200(name, tmp_path):
