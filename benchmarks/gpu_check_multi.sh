@@ -11,9 +11,9 @@ echo "== pytest multi ($N GPUs)"
 timeout 900 python -m pytest tests/test_gpu_multi.py -x -q > gpurun_out/pytest_multi_$TAG.log 2>&1; echo "pytest exit $?"; tail -30 gpurun_out/pytest_multi_$TAG.log
 echo "== sweep all_reduce variants"
 rm -f gpurun_out/sweep_$TAG.jsonl
-timeout 600 python benchmarks/sweep.py --gpus $N --colls all_reduce --algos all --min-bytes 1K --max-bytes 1G --factor 8 --out gpurun_out/sweep_$TAG.jsonl 2> gpurun_out/sweep_$TAG.err | tail -60; tail -5 gpurun_out/sweep_$TAG.err
+timeout 600 python benchmarks/sweep.py --gpus $N --colls all_reduce --algos all --graph --min-bytes 8 --max-bytes 1G --factor 8 --out gpurun_out/sweep_$TAG.jsonl 2> gpurun_out/sweep_$TAG.err | tail -60; tail -5 gpurun_out/sweep_$TAG.err
 echo "== sweep other collectives"
-timeout 600 python benchmarks/sweep.py --gpus $N --colls reduce,broadcast,scatter,gather,all_gather --algos all --min-bytes 1K --max-bytes 256M --factor 16 --out gpurun_out/sweep_$TAG.jsonl 2>> gpurun_out/sweep_$TAG.err | tail -80; tail -5 gpurun_out/sweep_$TAG.err
+timeout 600 python benchmarks/sweep.py --gpus $N --colls reduce,broadcast,scatter,gather,all_gather --algos all --graph --min-bytes 64 --max-bytes 256M --factor 16 --out gpurun_out/sweep_$TAG.jsonl 2>> gpurun_out/sweep_$TAG.err | tail -80; tail -5 gpurun_out/sweep_$TAG.err
 echo "== bench pdcc N=$N"
 timeout 600 python bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_pdcc_$TAG.json 2> gpurun_out/bench_pdcc_$TAG.err; echo "bench exit $?"; cat gpurun_out/bench_pdcc_$TAG.json; grep -v Warning gpurun_out/bench_pdcc_$TAG.err | tail -5
 echo "== bench reference N=$N"

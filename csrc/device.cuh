@@ -231,19 +231,42 @@ __device__ __forceinline__ void wait(const Ctx& c, int chan, uint32_t val, uint3
 
 enum Ld : int { LD_USER = 0, LD_SYS = 1 };
 
+// LD_SYS marks a source that peers wrote (a slot of this rank's block). It used to be a
+// strong system-scope load; those measured 2-3x slower than weak ones, and are not needed:
+// every consumer runs after a flag wait whose fence.acq_rel.sys already invalidated L1,
+// and slot loads never allocate in L1. Both kinds are the same instruction now; the tag
+// stays for readability and for the 4-byte fallback path.
 template <int LD>
 __device__ __forceinline__ uint4 ld16(const void* p) {
-  if constexpr (LD == LD_USER) return ld_stream_v4(p);
-  else return ld_sys_v4(p);
+  return ld_stream_v4(p);
 }
 
 __device__ __forceinline__ bool aligned16(const void* p) {
   return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }
 
-// CTA-wide copy of n bytes. Fast path: both sides 16-byte aligned, UNROLL independent
-// 16-byte loads in flight per thread. Anything else degrades to 4- or 1-byte words;
-// that only happens for odd user views (arena-side addresses are always aligned).
+// The hot loops live in __noinline__ functions: each gets its own register allocation with
+// only its few arguments live, instead of competing with everything the (heavily inlined,
+// four-ops-in-one) kernel body keeps alive. The call costs nothing next to a tile.
+
+// 16-byte vector copy of n16 units, UNROLL independent loads in flight per thread.
+template <int UNROLL>
+__device__ __noinline__ void copy16(char* __restrict__ d, const char* __restrict__ s, size_t n16) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const size_t pass = size_t(nt) * UNROLL;
+  const size_t nmain = n16 / pass * pass;
+  for (size_t i = tid; i < nmain; i += pass) {
+    uint4 v[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) v[k] = ld_stream_v4(s + ((i + size_t(k) * nt) << 4));
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) st_v4(d + ((i + size_t(k) * nt) << 4), v[k]);
+  }
+  for (size_t i = nmain + tid; i < n16; i += nt) st_v4(d + (i << 4), ld_stream_v4(s + (i << 4)));
+}
+
+// CTA-wide copy of n bytes. Fast path: both sides 16-byte aligned. Anything else degrades
+// to 4- or 1-byte words; that only happens for odd user views (slot addresses are aligned).
 template <int LD, int UNROLL>
 __device__ __forceinline__ void copy_bytes(void* dst, const void* src, size_t n) {
   const int tid = threadIdx.x, nt = blockDim.x;
@@ -251,84 +274,89 @@ __device__ __forceinline__ void copy_bytes(void* dst, const void* src, size_t n)
   const char* s = static_cast<const char*>(src);
   if (aligned16(d) && aligned16(s)) {
     const size_t n16 = n >> 4;
-    for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
-      uint4 v[UNROLL];
-#pragma unroll
-      for (int k = 0; k < UNROLL; ++k) {
-        size_t j = i + size_t(k) * nt;
-        if (j < n16) v[k] = ld16<LD>(s + (j << 4));
-      }
-#pragma unroll
-      for (int k = 0; k < UNROLL; ++k) {
-        size_t j = i + size_t(k) * nt;
-        if (j < n16) st_v4(d + (j << 4), v[k]);
-      }
-    }
+    copy16<UNROLL>(d, s, n16);
     for (size_t i = (n16 << 4) + tid; i < n; i += nt) d[i] = s[i];
   } else if (((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(s)) & 3u) == 0) {
     const size_t n4 = n >> 2;
     const uint32_t* s4 = reinterpret_cast<const uint32_t*>(s);
     uint32_t* d4 = reinterpret_cast<uint32_t*>(d);
-    for (size_t i = tid; i < n4; i += nt) {
-      uint32_t v;
-      if constexpr (LD == LD_SYS) v = ld_relaxed_sys(s4 + i);
-      else v = s4[i];
-      d4[i] = v;
-    }
+    for (size_t i = tid; i < n4; i += nt) d4[i] = s4[i];
     for (size_t i = (n4 << 2) + tid; i < n; i += nt) d[i] = s[i];
   } else {
-    for (size_t i = tid; i < n; i += nt) {
-      if constexpr (LD == LD_SYS) d[i] = *reinterpret_cast<const volatile char*>(s + i);
-      else d[i] = s[i];
-    }
+    for (size_t i = tid; i < n; i += nt) d[i] = s[i];
   }
 }
 
-// CTA-wide push of n bytes from `src` into the same slot offset of every rank in `mask`
-// (P2P stores) or into the multicast alias (one multimem.st per 16 bytes). `src` must be
-// 16-byte aligned; n is rounded up to 16 (slots have room).
-template <int LD, int UNROLL>
-__device__ __forceinline__ void push_p2p(const Ctx& c, size_t off, const void* src, size_t n,
-                                         uint32_t mask) {
+// CTA-wide push of n bytes from `src` (16-byte aligned) into the same slot offset of every
+// rank in `mask` (P2P stores). n is rounded up to 16 (slots have room).
+template <int UNROLL>
+__device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nranks, uint32_t mask,
+                                        size_t off, const char* __restrict__ s, size_t n16) {
   const int tid = threadIdx.x, nt = blockDim.x;
-  const char* s = static_cast<const char*>(src);
-  const size_t n16 = (n + 15) >> 4;
-  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
-    uint4 v[UNROLL];
+  if ((mask & (mask - 1u)) == 0) {  // one target: scatter, gather, reduce-scatter phase
+    char* d = base[__ffs(int(mask)) - 1] + off;
+    const size_t pass = size_t(nt) * UNROLL;
+    const size_t nmain = n16 / pass * pass;
+    for (size_t i = tid; i < nmain; i += pass) {
+      uint4 v[UNROLL];
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      size_t j = i + size_t(k) * nt;
-      if (j < n16) v[k] = ld16<LD>(s + (j << 4));
+      for (int k = 0; k < UNROLL; ++k) v[k] = ld_stream_v4(s + ((i + size_t(k) * nt) << 4));
+#pragma unroll
+      for (int k = 0; k < UNROLL; ++k) st_v4(d + ((i + size_t(k) * nt) << 4), v[k]);
+    }
+    for (size_t i = nmain + tid; i < n16; i += nt) st_v4(d + (i << 4), ld_stream_v4(s + (i << 4)));
+    return;
+  }
+  // several targets: every loaded unit is stored to each of them
+  constexpr int U2 = 4;
+  for (size_t i = tid; i < n16; i += size_t(nt) * U2) {
+    uint4 v[U2];
+#pragma unroll
+    for (int k = 0; k < U2; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      v[k] = ld_stream_v4(s + ((j < n16 ? j : i) << 4));
     }
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      size_t j = i + size_t(k) * nt;
-      if (j < n16) {
-        for (int p = 0; p < c.n; ++p)
-          if ((mask >> p) & 1u) st_v4(c.peer(p, off) + (j << 4), v[k]);
+    for (int p = 0; p < PDCC_MAX_RANKS; ++p) {
+      if (p < nranks && ((mask >> p) & 1u)) {
+        char* d = base[p] + off;
+#pragma unroll
+        for (int k = 0; k < U2; ++k) {
+          const size_t j = i + size_t(k) * nt;
+          if (j < n16) st_v4(d + (j << 4), v[k]);
+        }
       }
     }
   }
 }
 
 template <int LD, int UNROLL>
-__device__ __forceinline__ void push_mc(const Ctx& c, size_t off, const void* src, size_t n) {
+__device__ __forceinline__ void push_p2p(const Ctx& c, size_t off, const void* src, size_t n,
+                                         uint32_t mask) {
+  push16_p2p<UNROLL>(c.a->comm.base, c.n, mask, off, static_cast<const char*>(src), (n + 15) >> 4);
+}
+
+// Same through the multicast alias: one multimem.st per 16 bytes reaches every rank.
+template <int UNROLL>
+__device__ __noinline__ void push16_mc(char* __restrict__ d, const char* __restrict__ s,
+                                       size_t n16) {
   const int tid = threadIdx.x, nt = blockDim.x;
-  const char* s = static_cast<const char*>(src);
-  const size_t n16 = (n + 15) >> 4;
-  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
+  const size_t pass = size_t(nt) * UNROLL;
+  const size_t nmain = n16 / pass * pass;
+  for (size_t i = tid; i < nmain; i += pass) {
     uint4 v[UNROLL];
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      size_t j = i + size_t(k) * nt;
-      if (j < n16) v[k] = ld16<LD>(s + (j << 4));
-    }
+    for (int k = 0; k < UNROLL; ++k) v[k] = ld_stream_v4(s + ((i + size_t(k) * nt) << 4));
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) {
-      size_t j = i + size_t(k) * nt;
-      if (j < n16) multimem_st_v4(c.mc(off) + (j << 4), v[k]);
-    }
+    for (int k = 0; k < UNROLL; ++k) multimem_st_v4(d + ((i + size_t(k) * nt) << 4), v[k]);
   }
+  for (size_t i = nmain + tid; i < n16; i += nt)
+    multimem_st_v4(d + (i << 4), ld_stream_v4(s + (i << 4)));
+}
+
+template <int LD, int UNROLL>
+__device__ __forceinline__ void push_mc(const Ctx& c, size_t off, const void* src, size_t n) {
+  push16_mc<UNROLL>(c.mc(off), static_cast<const char*>(src), (n + 15) >> 4);
 }
 
 }  // namespace pdcc

@@ -52,18 +52,23 @@ struct Geo {
 struct Prologue {
   uint32_t g0;
   int poison;
-  RankArgs args;  // emulation only: this virtual rank's args
+  RankArgs args;  // this (virtual) rank's args: shared memory => LDS, not generic loads
 };
 
 __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
-  const RankArgs* a = &k.r;
-  if (k.emu != nullptr) {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(k.emu + blockIdx.y);
+  {
     uint32_t* dst = reinterpret_cast<uint32_t*>(&sh.args);
-    for (int i = threadIdx.x; i < int(sizeof(RankArgs) / 4); i += blockDim.x) dst[i] = src[i];
+    constexpr int kWords = int(sizeof(RankArgs) / 4);
+    if (k.emu != nullptr) {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(k.emu + blockIdx.y);
+      for (int i = threadIdx.x; i < kWords; i += blockDim.x) dst[i] = src[i];
+    } else {
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(&k.r);
+      for (int i = threadIdx.x; i < kWords; i += blockDim.x) dst[i] = src[i];
+    }
     __syncthreads();
-    a = &sh.args;
   }
+  const RankArgs* a = &sh.args;
   c.a = a;
   c.rank = a->comm.rank;
   c.n = a->comm.nranks;
@@ -130,10 +135,136 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
 // ---------------------------------------------------------------------------------------
 enum ArAlgo : int { AR_ONESHOT_P2P, AR_TWOSHOT_P2P, AR_ONESHOT_NVLS, AR_TWOSHOT_NVLS, AR_LL };
 
+// Byte-exact 16-byte unit access on a user tensor range (ragged tail / odd views).
+__device__ __forceinline__ uint4 load_user_unit(const char* base, uint64_t len, size_t j) {
+  const char* p = base + (uint64_t(j) << 4);
+  const uint64_t left = len - (uint64_t(j) << 4);
+  if (left >= 16 && aligned16(p)) return ld_stream_v4(p);
+  union {
+    uint4 v;
+    unsigned char b[16];
+  } u;
+  u.v = make_uint4(0, 0, 0, 0);
+  const int nb = left < 16 ? int(left) : 16;
+  for (int i = 0; i < nb; ++i) u.b[i] = static_cast<unsigned char>(p[i]);
+  return u.v;
+}
+
+__device__ __forceinline__ void store_user_unit(char* base, uint64_t len, size_t j,
+                                                const uint4& v) {
+  char* p = base + (uint64_t(j) << 4);
+  const uint64_t left = len - (uint64_t(j) << 4);
+  if (left >= 16 && aligned16(p)) {
+    st_v4(p, v);
+    return;
+  }
+  union {
+    uint4 v;
+    unsigned char b[16];
+  } u;
+  u.v = v;
+  const int nb = left < 16 ? int(left) : 16;
+  for (int i = 0; i < nb; ++i) p[i] = static_cast<char>(u.b[i]);
+}
+
+// Push `len` bytes of a user tensor into slot offset `dst_off` of the ranks in `mask` (P2P
+// stores) or of everyone (MC: one multimem.st per 16 bytes). A 16-byte aligned source
+// whose length is a multiple of 16 streams straight from the user tensor; anything else
+// is staged through `stage_off` of this rank's own slot first.
+template <bool MC>
+__device__ __forceinline__ void push_user(const Ctx& c, const char* src, uint64_t len,
+                                          size_t dst_off, size_t stage_off, uint32_t mask) {
+  if (len == 0) return;
+  if (aligned16(src) && (len & 15u) == 0) {
+    if constexpr (MC) push_mc<LD_USER, 8>(c, dst_off, src, len);
+    else push_p2p<LD_USER, 8>(c, dst_off, src, len, mask);
+  } else {
+    copy_bytes<LD_USER, 4>(c.mine(stage_off), src, len);
+    __syncthreads();
+    if constexpr (MC) push_mc<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len);
+    else push_p2p<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len, mask);
+    __syncthreads();
+  }
+}
+
+// Hot loop of every P2P reduction: whole passes of nt*U units, no bounds checks, every load
+// unconditional (ranks q >= n alias my own operand and are skipped in the combine), all
+// loads local. Operand q comes from the user tensor (q == rank) or from A[q] of my slot;
+// combined in rank order 0..n-1 on every rank => bitwise identical results everywhere.
+//   out   : user tensor position of unit 0, or nullptr when this rank does not keep it
+//   base  : peers' block bases (shared memory); push_mask: ranks whose B[me] gets the result
+template <typename T, int OP, bool WIDE, bool TWOSHOT, int NP, int U>
+__device__ __noinline__ void combine_main(const char* __restrict__ user,
+                                          const char* __restrict__ slot_a, size_t a_stride,
+                                          size_t nmain, void* __restrict__ out, float scale,
+                                          int rank, int n, char* const* __restrict__ base,
+                                          size_t b_off, uint32_t push_mask) {
+  using Tr = Traits<T>;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const size_t pass = size_t(nt) * U;
+  const bool scaled = scale != 1.0f;
+  for (size_t j0 = tid; j0 < nmain; j0 += pass) {
+    uint4 v[U][NP];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = j0 + size_t(u) * nt;
+#pragma unroll
+      for (int q = 0; q < NP; ++q) {
+        const char* sq = (q == rank || q >= n) ? user : slot_a + size_t(q) * a_stride;
+        v[u][q] = ld_stream_v4(sq + (j << 4));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = j0 + size_t(u) * nt;
+      Acc<T> acc;
+      acc.init(v[u][0]);
+#pragma unroll
+      for (int q = 1; q < NP; ++q)
+        if (q < n) acc.template add<OP>(v[u][q]);
+      if (scaled) acc.scale(scale);
+      if constexpr (TWOSHOT) {
+        const uint4 res = acc.pack();
+#pragma unroll
+        for (int p = 0; p < NP; ++p)
+          if ((push_mask >> p) & 1u) st_v4(base[p] + b_off + (j << 4), res);
+        if constexpr (WIDE) acc.init(res);  // every rank must see the same rounded value
+      }
+      if (out != nullptr) {
+        if constexpr (WIDE) {
+          float* o = static_cast<float*>(out) + j * Tr::K;
+#pragma unroll
+          for (int i = 0; i < Tr::K; i += 4) {
+            uint4 w;
+            float* f = reinterpret_cast<float*>(&w);
+            f[0] = float(acc.v[i]); f[1] = float(acc.v[i + 1]);
+            f[2] = float(acc.v[i + 2]); f[3] = float(acc.v[i + 3]);
+            st_v4(o + i, w);
+          }
+        } else {
+          st_v4(static_cast<T*>(out) + j * Tr::K, acc.pack());
+        }
+      }
+    }
+  }
+}
+
+// Slot layouts (offsets from the tile's slot, `tile` = KArgs::tile_bytes, `sub` = tile/n):
+//   one-shot P2P  A[q] at q*stride            rank q's whole tile        (tile <= slot/n)
+//   two-shot P2P  A[q] at q*sub               rank q's partial of MY chunk
+//                 B[j] at tile + j*sub        reduced chunk j from its owner  (tile <= slot/2)
+//   NVLS          the tile itself at 0        (multicast-addressable copy-in)
+//
+// The P2P variants are write-based: every byte that crosses NVLink is a posted store issued
+// straight from the user tensor (IN) or from registers (MID); all loads are local. Remote
+// loads cost a round trip per 16 bytes and measured 2-3x slower than stores on B200
+// (profiles/sweep_n2_pull_vs_push.md), so nothing here pulls.
 template <typename T, bool WIDE, int OP, int ALGO, bool ROOTED>
 struct ReducePolicy {
   using Tr = Traits<T>;
-  static constexpr bool kHasOut = (ALGO == AR_TWOSHOT_P2P || ALGO == AR_TWOSHOT_NVLS);
+  static constexpr bool kTwoShot = (ALGO == AR_TWOSHOT_P2P || ALGO == AR_TWOSHOT_NVLS);
+  static constexpr bool kNvls = (ALGO == AR_ONESHOT_NVLS || ALGO == AR_TWOSHOT_NVLS);
+  static constexpr bool kHasOut = kTwoShot;
   static constexpr int kMm = MmFor<T, OP>::kind;
 
   const KArgs& k;
@@ -145,70 +276,110 @@ struct ReducePolicy {
     geo = Geo{k.bytes, k.tile_bytes, int(gridDim.x), c.b};
     all = (1u << c.n) - 1u;
   }
-  __device__ __forceinline__ uint32_t ready_to() const { return ROOTED ? (1u << k.root) : all; }
+  // one-shot rooted reduce: only the root consumes, so only the root is signalled
+  __device__ __forceinline__ uint32_t ready_to() const {
+    return (ROOTED && !kTwoShot) ? (1u << k.root) : all;
+  }
   __device__ __forceinline__ uint32_t ready_from() const {
-    return ROOTED ? (c.rank == k.root ? all : 0u) : all;
+    return (ROOTED && !kTwoShot) ? (c.rank == k.root ? all : 0u) : all;
+  }
+  __device__ __forceinline__ size_t sub_bytes() const { return size_t(k.tile_bytes / c.n); }
+  // bytes of chunk q inside a tile of `len` valid bytes
+  __device__ __forceinline__ uint64_t chunk_len(uint64_t len, int q) const {
+    const uint64_t lo = uint64_t(q) * sub_bytes();
+    if (len <= lo) return 0;
+    return len - lo < sub_bytes() ? len - lo : sub_bytes();
   }
 
   __device__ __forceinline__ void in(int t) {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    copy_bytes<LD_USER, 4>(c.mine(c.slot_off(c.g0 + t)), static_cast<const char*>(c.a->in) + off,
-                           len);
-  }
-
-  // P2P: U units per thread per pass, every peer's 16-byte load issued before the first
-  // combine, so U x n loads are in flight per thread (NVLink round trips are ~2 us: one
-  // load in flight per thread would cap a GPU at ~150 GB/s). Peers are combined in rank
-  // order 0..n-1 on every rank => bitwise identical results.
-  template <int NP, int U, bool TWOSHOT>
-  __device__ __forceinline__ void mid_p2p(size_t so, size_t lo, size_t hi, size_t nelem,
-                                          size_t elem0) {
-    const int tid = threadIdx.x, nt = blockDim.x;
-    const bool scaled = k.scale != 1.0f;
-    for (size_t j0 = lo + tid; j0 < hi; j0 += size_t(nt) * U) {
-      uint4 v[U][NP];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const size_t j = j0 + size_t(u) * nt;
-        if (j < hi) {
-#pragma unroll
-          for (int p = 0; p < NP; ++p)
-            if (p < c.n) v[u][p] = ld_sys_v4(c.peer(p, so) + (j << 4));
-        }
+    const size_t so = c.slot_off(c.g0 + t);
+    const char* src = static_cast<const char*>(c.a->in) + off;
+    if constexpr (kNvls) {
+      copy_bytes<LD_USER, 8>(c.mine(so), src, len);
+    } else if constexpr (ALGO == AR_ONESHOT_P2P) {
+      const size_t mine_off = so + size_t(c.rank) * k.stride;
+      if constexpr (ROOTED) {
+        if (c.rank != k.root) push_user<false>(c, src, len, mine_off, mine_off, 1u << k.root);
+      } else {
+        push_user<false>(c, src, len, mine_off, mine_off, all & ~(1u << c.rank));
       }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const size_t j = j0 + size_t(u) * nt;
-        if (j < hi) {
-          Acc<T> acc;
-          acc.init(v[u][0]);
-#pragma unroll
-          for (int p = 1; p < NP; ++p)
-            if (p < c.n) acc.template add<OP>(v[u][p]);
-          if (scaled) acc.scale(k.scale);
-          if constexpr (TWOSHOT) {
-            const uint4 res = acc.pack();
-#pragma unroll
-            for (int p = 0; p < NP; ++p)
-              if (p < c.n) st_v4(c.peer(p, so) + (j << 4), res);
-          } else {
-            const size_t e = j * Tr::K;
-            const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
-            store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
-          }
-        }
+    } else {  // two-shot P2P: my partial of chunk p goes to its owner p
+      const size_t sub = sub_bytes();
+      for (int i = 1; i < c.n; ++i) {
+        const int p = (c.rank + i) % c.n;
+        push_user<false>(c, src + size_t(p) * sub, chunk_len(len, p), so + size_t(c.rank) * sub,
+                         so + k.tile_bytes + size_t(p) * sub, 1u << p);
       }
     }
   }
 
-  template <bool TWOSHOT>
-  __device__ __forceinline__ void mid_p2p_dispatch(size_t so, size_t lo, size_t hi, size_t nelem,
-                                                   size_t elem0) {
-    if (c.n <= 2) mid_p2p<2, 8, TWOSHOT>(so, lo, hi, nelem, elem0);
-    else if (c.n <= 4) mid_p2p<4, 4, TWOSHOT>(so, lo, hi, nelem, elem0);
-    else mid_p2p<8, 2, TWOSHOT>(so, lo, hi, nelem, elem0);
+  // Combine `nunits` 16-byte units: rank q's operand comes from the user tensor (q == me)
+  // or from A[q] of my own slot, in rank order 0..n-1 on every rank (bitwise identical
+  // results). The bulk runs a branch-free loop with U x n vector loads issued before the
+  // first combine; a ragged last unit or an odd user view falls to a compact scalar-safe
+  // loop (one unit at a time) so the fast loop stays in registers.
+  //   write_out : the result goes to the user tensor (always for one-shot; owner's own
+  //               chunk for two-shot; only on the root when ROOTED)
+  //   push_mask : two-shot: ranks whose B[me] receives the packed result
+  template <int NP, int U>
+  __device__ __forceinline__ void combine_units(const char* user, uint64_t user_len, size_t a_off,
+                                                size_t a_stride, size_t nunits, size_t elem0,
+                                                bool write_out, size_t b_off, uint32_t push_mask) {
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const bool scaled = k.scale != 1.0f;
+    const size_t nelem = user_len / sizeof(T);
+    using Out = typename std::conditional<WIDE, float, T>::type;
+    Out* outp = static_cast<Out*>(c.a->out) + elem0;
+    const bool fast = aligned16(user) && (!write_out || aligned16(outp));
+    const size_t nfast = fast ? size_t(user_len >> 4) : 0;
+
+    // Operand/peer addresses are recomputed from two bases instead of being held in
+    // 2 x NP pointer registers: all loads are local (HBM latency, not NVLink), so register
+    // room is better spent on the U x NP vectors in flight.
+    const char* slot_a = c.mine(a_off);
+
+    const size_t pass = size_t(nt) * U;
+    const size_t nmain = nfast / pass * pass;
+    if (nmain)
+      combine_main<T, OP, WIDE, kTwoShot, NP, U>(user, slot_a, a_stride, nmain,
+                                                 write_out ? static_cast<void*>(outp) : nullptr,
+                                                 k.scale, c.rank, c.n, c.a->comm.base, b_off,
+                                                 push_mask);
+
+    // remainder, ragged tail, odd views: one unit per thread per pass, byte-exact on the
+    // user side (load_user_unit / store_unit take their vector path when they can)
+    for (size_t j = nmain + tid; j < nunits; j += nt) {
+      Acc<T> acc;
+      for (int q = 0; q < c.n; ++q) {
+        const uint4 v = q == c.rank
+                            ? load_user_unit(user, user_len, j)
+                            : ld_stream_v4(c.mine(a_off + size_t(q) * a_stride) + (j << 4));
+        if (q == 0) acc.init(v);
+        else acc.template add<OP>(v);
+      }
+      if (scaled) acc.scale(k.scale);
+      if constexpr (kTwoShot) {
+        const uint4 res = acc.pack();
+        for (int p = 0; p < c.n; ++p)
+          if ((push_mask >> p) & 1u) st_v4(c.peer(p, b_off) + (j << 4), res);
+        if constexpr (WIDE) acc.init(res);
+      }
+      if (write_out) {
+        const size_t e = j * Tr::K;
+        const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
+        store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
+      }
+    }
+  }
+
+  template <typename... A>
+  __device__ __forceinline__ void combine_dispatch(A... a) {
+    if (c.n <= 2) combine_units<2, 4>(a...);
+    else if (c.n <= 4) combine_units<4, 2>(a...);
+    else combine_units<8, 1>(a...);
   }
 
   // NVLS: the switch reduces; 8 multimem.ld_reduce in flight per thread.
@@ -254,7 +425,6 @@ struct ReducePolicy {
   }
 
   __device__ __forceinline__ void mid(int t) {
-    if (ROOTED && c.rank != k.root) return;
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
@@ -262,19 +432,50 @@ struct ReducePolicy {
     const size_t n16 = (len + 15) >> 4;
     const size_t nelem = len / sizeof(T);
     const size_t elem0 = off / sizeof(T);
+    const char* src = static_cast<const char*>(c.a->in) + off;
     if constexpr (ALGO == AR_ONESHOT_P2P) {
-      mid_p2p_dispatch<false>(so, 0, n16, nelem, elem0);
+      if (ROOTED && c.rank != k.root) return;
+      combine_dispatch(src, len, so, size_t(k.stride), n16, elem0, true, size_t(0), 0u);
     } else if constexpr (ALGO == AR_ONESHOT_NVLS) {
+      if (ROOTED && c.rank != k.root) return;
       mid_nvls<false>(so, 0, n16, nelem, elem0);
+    } else if constexpr (ALGO == AR_TWOSHOT_P2P) {
+      // I own chunk `me` of the tile: combine the partials in A, write my part of the
+      // result and hand the reduced chunk to everyone who needs it (B[me] on their side).
+      const size_t sub = sub_bytes();
+      const uint64_t clen = chunk_len(len, c.rank);
+      if (clen == 0) return;
+      const uint32_t others = all & ~(1u << c.rank);
+      const uint32_t push_mask = ROOTED ? (c.rank == k.root ? 0u : (1u << k.root)) : others;
+      const bool write_out = !ROOTED || c.rank == k.root;
+      combine_dispatch(src + size_t(c.rank) * sub, clen, so, sub, size_t((clen + 15) >> 4),
+                       elem0 + size_t(c.rank) * sub / sizeof(T), write_out,
+                       so + size_t(k.tile_bytes) + size_t(c.rank) * sub, push_mask);
     } else {
-      // two-shot: this rank owns units [lo, hi) of the tile
+      // NVLS two-shot: this rank owns units [lo, hi) of the tile
       const size_t sub16 = (k.tile_bytes / c.n) >> 4;
       const size_t lo = size_t(c.rank) * sub16;
       size_t hi = lo + sub16;
       if (hi > n16) hi = n16;
-      if (lo < hi) {
-        if constexpr (ALGO == AR_TWOSHOT_P2P) mid_p2p_dispatch<true>(so, lo, hi, nelem, elem0);
-        else mid_nvls<true>(so, lo, hi, nelem, elem0);
+      if (lo < hi) mid_nvls<true>(so, lo, hi, nelem, elem0);
+    }
+  }
+
+  // slot bytes -> user tensor, widening 16-bit floats to fp32 when WIDE
+  __device__ __forceinline__ void copy_out(const char* slot, uint64_t byte_off, uint64_t len) {
+    if constexpr (!WIDE) {
+      copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + byte_off, slot, len);
+    } else {
+      const int tid = threadIdx.x, nt = blockDim.x;
+      const size_t n16 = (len + 15) >> 4;
+      const size_t nelem = len / sizeof(T);
+      const size_t elem0 = byte_off / sizeof(T);
+      for (size_t j = tid; j < n16; j += nt) {
+        Acc<T> acc;
+        acc.init(ld_stream_v4(slot + (j << 4)));
+        const size_t e = j * Tr::K;
+        const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
+        store_unit<T, true>(c.a->out, elem0 + e, acc, valid);
       }
     }
   }
@@ -283,21 +484,17 @@ struct ReducePolicy {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    const char* slot = c.mine(c.slot_off(c.g0 + t));
-    if constexpr (!WIDE) {
-      copy_bytes<LD_SYS, 4>(static_cast<char*>(c.a->out) + off, slot, len);
-    } else {
-      const int tid = threadIdx.x, nt = blockDim.x;
-      const size_t n16 = (len + 15) >> 4;
-      const size_t nelem = len / sizeof(T);
-      const size_t elem0 = off / sizeof(T);
-      for (size_t j = tid; j < n16; j += nt) {
-        Acc<T> acc;
-        acc.init(ld_sys_v4(slot + (j << 4)));
-        const size_t e = j * Tr::K;
-        const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
-        store_unit<T, true>(c.a->out, elem0 + e, acc, valid);
+    const size_t so = c.slot_off(c.g0 + t);
+    if constexpr (ALGO == AR_TWOSHOT_P2P) {
+      if (ROOTED && c.rank != k.root) return;
+      const size_t sub = sub_bytes();
+      for (int i = 1; i < c.n; ++i) {
+        const int j = (c.rank + i) % c.n;
+        const uint64_t clen = chunk_len(len, j);
+        if (clen) copy_out(c.mine(so + size_t(k.tile_bytes) + size_t(j) * sub), off + size_t(j) * sub, clen);
       }
+    } else {
+      copy_out(c.mine(so), off, len);
     }
   }
 };
@@ -359,23 +556,10 @@ struct MovePolicy {
     else return all;
   }
 
-  // Push `len` bytes of a user tensor to slot offset `dst_off` of the ranks in `mask`
-  // (or of everyone through the multicast alias). A 16-byte aligned, 16-byte multiple
-  // source streams straight from the user tensor; anything else is staged through
-  // `stage_off` of this rank's own slot first.
   template <bool MC>
   __device__ __forceinline__ void push(const char* src, uint64_t len, size_t dst_off,
                                        size_t stage_off, uint32_t mask) {
-    if (aligned16(src) && (len & 15u) == 0) {
-      if constexpr (MC) push_mc<LD_USER, 8>(c, dst_off, src, len);
-      else push_p2p<LD_USER, 8>(c, dst_off, src, len, mask);
-    } else {
-      copy_bytes<LD_USER, 4>(c.mine(stage_off), src, len);
-      __syncthreads();
-      if constexpr (MC) push_mc<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len);
-      else push_p2p<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len, mask);
-      __syncthreads();
-    }
+    push_user<MC>(c, src, len, dst_off, stage_off, mask);
   }
 
   __device__ __forceinline__ void in(int t) {

@@ -149,14 +149,22 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
     }
   } else if (op.coll == PDCC_REDUCE) {
     const bool nvls = mc_ok && nvls_reducible(op.dtype, redop);
-    if (algo == PDCC_ALGO_AUTO) algo = nvls ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
     if (algo == PDCC_ALGO_ONESHOT_P2P) algo = PDCC_ALGO_P2P;
     if (algo == PDCC_ALGO_ONESHOT_NVLS) algo = PDCC_ALGO_NVLS;
+    if (algo == PDCC_ALGO_AUTO) {
+      // Root ingress: NVLS S (the switch reduces), one-shot push (n-1)S, two-phase push
+      // (reduce-scatter among all ranks, then the owners hand their chunk to the root)
+      // 2S(n-1)/n. Two-phase only pays from n = 3 and once the extra flag round is amortised.
+      if (nvls && n >= 4) algo = PDCC_ALGO_NVLS;
+      else if (n > 2 && bytes > uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10)))
+        algo = PDCC_ALGO_TWOSHOT_P2P;
+      else algo = PDCC_ALGO_P2P;
+    }
     if (algo == PDCC_ALGO_NVLS && !nvls) {
       set_error("NVLS reduce not available for dtype %d op %d", op.dtype, redop);
       return PDCC_EUNSUPPORTED;
     }
-    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS) {
+    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS && algo != PDCC_ALGO_TWOSHOT_P2P) {
       set_error("algo %d is not a reduce algorithm", algo);
       return PDCC_EINVAL;
     }
@@ -187,11 +195,14 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   // cap: payload one CTA may place in one slot for this collective
   uint64_t cap = comm.slot_bytes;
   uint64_t align = 16;
-  const bool sub_slots = op.coll == PDCC_GATHER ||
+  const bool reduce_coll = op.coll == PDCC_ALL_REDUCE || op.coll == PDCC_REDUCE;
+  const bool oneshot_push = reduce_coll && (algo == PDCC_ALGO_ONESHOT_P2P || algo == PDCC_ALGO_P2P);
+  const bool twoshot_push = reduce_coll && algo == PDCC_ALGO_TWOSHOT_P2P;
+  const bool sub_slots = op.coll == PDCC_GATHER || oneshot_push ||
                          (op.coll == PDCC_ALL_GATHER && algo == PDCC_ALGO_NVLS);
-  if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);
-  if (op.coll == PDCC_ALL_REDUCE &&
-      (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS)) {
+  if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);  // one sub-slot per source rank
+  if (twoshot_push) cap = comm.slot_bytes / 2;                 // partials + reduced chunks
+  if (twoshot_push || (op.coll == PDCC_ALL_REDUCE && algo == PDCC_ALGO_TWOSHOT_NVLS)) {
     align = 16 * uint64_t(n);
     cap = cap / align * align;
   }
@@ -282,9 +293,10 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
         return PDCC_EINVAL;
       }
       fn = reduce_kernel_for(op.dtype, false,
-                             plan.algo == PDCC_ALGO_LL     ? AR_LL
-                             : plan.algo == PDCC_ALGO_NVLS ? AR_ONESHOT_NVLS
-                                                           : AR_ONESHOT_P2P,
+                             plan.algo == PDCC_ALGO_LL            ? AR_LL
+                             : plan.algo == PDCC_ALGO_NVLS        ? AR_ONESHOT_NVLS
+                             : plan.algo == PDCC_ALGO_TWOSHOT_P2P ? AR_TWOSHOT_P2P
+                                                                  : AR_ONESHOT_P2P,
                              true);
       break;
     case PDCC_BROADCAST:

@@ -61,39 +61,6 @@ __device__ __forceinline__ uint4 ld_ll(const Ctx& c, const char* src, uint32_t f
   return make_uint4(a.x, a.z, b.x, b.z);
 }
 
-// Byte-exact access to unit j of a user tensor range [base, base+len): full aligned units
-// go as one 16-byte access, the ragged tail or an odd view byte by byte.
-__device__ __forceinline__ uint4 load_user_unit(const char* base, uint64_t len, uint32_t j) {
-  const char* p = base + (uint64_t(j) << 4);
-  const uint64_t left = len - (uint64_t(j) << 4);
-  if (left >= 16 && aligned16(p)) return ld_stream_v4(p);
-  union {
-    uint4 v;
-    unsigned char b[16];
-  } u;
-  u.v = make_uint4(0, 0, 0, 0);
-  const int nb = left < 16 ? int(left) : 16;
-  for (int i = 0; i < nb; ++i) u.b[i] = static_cast<unsigned char>(p[i]);
-  return u.v;
-}
-
-__device__ __forceinline__ void store_user_unit(char* base, uint64_t len, uint32_t j,
-                                                const uint4& v) {
-  char* p = base + (uint64_t(j) << 4);
-  const uint64_t left = len - (uint64_t(j) << 4);
-  if (left >= 16 && aligned16(p)) {
-    st_v4(p, v);
-    return;
-  }
-  union {
-    uint4 v;
-    unsigned char b[16];
-  } u;
-  u.v = v;
-  const int nb = left < 16 ? int(left) : 16;
-  for (int i = 0; i < nb; ++i) p[i] = static_cast<char>(u.b[i]);
-}
-
 enum LLKind : int { LL_ALL_REDUCE, LL_REDUCE, LL_BROADCAST, LL_SCATTER, LL_GATHER, LL_ALL_GATHER };
 
 // One LL tile of collective KIND. T/OP/WIDE matter for the two reducing kinds only.
