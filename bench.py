@@ -203,8 +203,8 @@ def run(D, rank: int, size: int, args, launch_count) -> dict:
     lat = []
     for _ in range(5):
         D.all_reduce(small, op=D.ReduceOp.SUM, group=suite.group)
-    for _ in range(15):
-        lat.append(timed(lambda: D.all_reduce(small, op=D.ReduceOp.SUM, group=suite.group), 20))
+    for _ in range(9):
+        lat.append(timed(lambda: D.all_reduce(small, op=D.ReduceOp.SUM, group=suite.group), 200))
     small_p50 = statistics.median(lat) * 1e3
 
     # ---- end to end ------------------------------------------------------------------

@@ -160,6 +160,7 @@ def main() -> None:
                     algos += ["oneshot_nvls", "twoshot_nvls"]
             elif coll in ("reduce", "broadcast", "all_gather"):
                 algos = ["auto", "ll", "p2p"] + (["nvls"] if comm and comm.has_multicast else [])
+                algos += {"reduce": ["twoshot_p2p"], "all_gather": ["pull"]}.get(coll, [])
             else:
                 algos = ["auto", "ll", "p2p"]
         for nbytes in sizes:

@@ -293,6 +293,7 @@ template <int UNROLL>
 __device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nranks, uint32_t mask,
                                         size_t off, const char* __restrict__ s, size_t n16) {
   const int tid = threadIdx.x, nt = blockDim.x;
+  if (mask == 0) return;  // a group of one has nobody to push to
   if ((mask & (mask - 1u)) == 0) {  // one target: scatter, gather, reduce-scatter phase
     char* d = base[__ffs(int(mask)) - 1] + off;
     const size_t pass = size_t(nt) * UNROLL;

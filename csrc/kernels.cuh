@@ -174,7 +174,7 @@ __device__ __forceinline__ void store_user_unit(char* base, uint64_t len, size_t
 template <bool MC>
 __device__ __forceinline__ void push_user(const Ctx& c, const char* src, uint64_t len,
                                           size_t dst_off, size_t stage_off, uint32_t mask) {
-  if (len == 0) return;
+  if (len == 0 || (!MC && mask == 0)) return;
   if (aligned16(src) && (len & 15u) == 0) {
     if constexpr (MC) push_mc<LD_USER, 8>(c, dst_off, src, len);
     else push_p2p<LD_USER, 8>(c, dst_off, src, len, mask);
@@ -527,6 +527,7 @@ enum MoveKind : int {
   MV_SCATTER,         // main.py:37  root pushes list[j] into rank j's slot
   MV_GATHER,          // main.py:52  rank r pushes into sub-slot r of the root's slot
   MV_ALLGATHER_PULL,  // main.py:68  stage own shard, pull every peer's into list[p]
+  MV_ALLGATHER_PUSH,  // main.py:68  store own shard into sub-slot r of every peer
   MV_ALLGATHER_NVLS,  // main.py:68  multimem.st own shard into sub-slot r everywhere
   MV_BARRIER
 };
@@ -594,6 +595,11 @@ struct MovePolicy {
       const char* src = static_cast<const char*>(c.a->in) + off;
       const size_t sub = so + size_t(c.rank) * k.stride;
       push<true>(src, len, sub, sub, all);
+    } else if constexpr (KIND == MV_ALLGATHER_PUSH) {
+      const char* src = static_cast<const char*>(c.a->in) + off;
+      const size_t sub = so + size_t(c.rank) * k.stride;
+      push<false>(src, len, sub, sub, all & ~(1u << c.rank));
+      copy_bytes<LD_USER, 8>(static_cast<char*>(c.a->list[c.rank]) + off, src, len);
     }
   }
 
@@ -618,8 +624,14 @@ struct MovePolicy {
       }
     } else if constexpr (KIND == MV_ALLGATHER_NVLS) {
       for (int j = 0; j < c.n; ++j)
-        copy_bytes<LD_SYS, 4>(static_cast<char*>(c.a->list[j]) + off,
+        copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->list[j]) + off,
                               c.mine(so + size_t(j) * k.stride), len);
+    } else if constexpr (KIND == MV_ALLGATHER_PUSH) {
+      for (int i = 1; i < c.n; ++i) {
+        const int j = (c.rank + i) % c.n;
+        copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->list[j]) + off,
+                              c.mine(so + size_t(j) * k.stride), len);
+      }
     }
   }
   __device__ __forceinline__ void out(int) {}

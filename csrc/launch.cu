@@ -55,6 +55,7 @@ static KernelFn move_kernel_for(int kind) {
     case MV_GATHER: return move_kernel<MV_GATHER>;
     case MV_ALLGATHER_PULL: return move_kernel<MV_ALLGATHER_PULL>;
     case MV_ALLGATHER_NVLS: return move_kernel<MV_ALLGATHER_NVLS>;
+    case MV_ALLGATHER_PUSH: return move_kernel<MV_ALLGATHER_PUSH>;
     case MV_BARRIER: return move_kernel<MV_BARRIER>;
     default: return nullptr;
   }
@@ -107,7 +108,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   // Small messages: flag-in-data push (ll.cuh). Above the threshold the doubled wire
   // bytes cost more than the fences they save. Thresholds from profiles/ sweeps.
   if (algo == PDCC_ALGO_AUTO && op.coll != PDCC_BARRIER && n > 1 &&
-      bytes <= uint64_t(env_int("PDCC_LL_MAX", 32 << 10)))
+      bytes <= uint64_t(env_int("PDCC_LL_MAX", (512 << 10) / n)))
     algo = PDCC_ALGO_LL;
   if (algo == PDCC_ALGO_LL) {
     if (op.coll == PDCC_BARRIER) {
@@ -129,14 +130,17 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
     if (algo == PDCC_ALGO_AUTO) {
       // One-shot moves N x bytes into every GPU but needs a single flag round; two-shot
       // moves ~2 x bytes and needs two. Crossover measured on 8xB200 (profiles/).
-      const uint64_t oneshot_max = nvls ? uint64_t(env_int("PDCC_ONESHOT_NVLS_MAX", 64 << 10))
-                                        : uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10));
-      // Link bytes per GPU and direction: NVLS two-shot S(1 + 1/n) (the switch reads all of
-      // my data once, I receive my shard and everyone's broadcast), P2P two-shot
-      // 2S(n-1)/n. The switch wins from n = 4 up.
-      if (nvls && n >= 4) algo = bytes <= oneshot_max ? PDCC_ALGO_ONESHOT_NVLS : PDCC_ALGO_TWOSHOT_NVLS;
-      else algo = (bytes <= uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10)) || n == 1)
-                      ? PDCC_ALGO_ONESHOT_P2P : PDCC_ALGO_TWOSHOT_P2P;
+      // Link bytes per GPU and direction: one-shot push (n-1)S, two-shot push 2S(n-1)/n,
+      // NVLS two-shot S(1 + 1/n) (the switch reads all of my data once; I receive my
+      // shard and everyone's broadcast). At n = 2 one-shot moves no more than two-shot and
+      // has one flag round less, so it wins at every size; the switch wins from n = 4 up.
+      if (n <= 2) {
+        algo = PDCC_ALGO_ONESHOT_P2P;
+      } else if (bytes <= uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 1 << 20))) {
+        algo = PDCC_ALGO_ONESHOT_P2P;
+      } else {
+        algo = (nvls && n >= 4) ? PDCC_ALGO_TWOSHOT_NVLS : PDCC_ALGO_TWOSHOT_P2P;
+      }
     }
     if ((algo == PDCC_ALGO_ONESHOT_NVLS || algo == PDCC_ALGO_TWOSHOT_NVLS) && !nvls) {
       set_error("NVLS all_reduce not available for dtype %d op %d (multicast %s)", op.dtype,
@@ -173,17 +177,18 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       if (op.coll == PDCC_BROADCAST) {
         algo = (mc_ok && n > 2) ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       } else {
-        // pull is ingress-bound exactly like the multicast push and writes the user
-        // list directly (no copy-out); the push wins only while latency dominates.
-        algo = (mc_ok && bytes <= uint64_t(env_int("PDCC_AG_NVLS_MAX", 32 << 10))) ? PDCC_ALGO_NVLS
-                                                                                   : PDCC_ALGO_P2P;
+        // Posted stores beat remote loads on NVLink (profiles/): push my shard into every
+        // peer's slot. From n = 4 one multimem.st replaces the n-1 stores (the echo of my
+        // own shard costs 1/n extra ingress, which is what makes it lose at n = 2).
+        algo = (mc_ok && n >= 4) ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       }
     }
     if (algo == PDCC_ALGO_NVLS && !mc_ok) {
       set_error("multicast not mapped for this comm");
       return PDCC_EUNSUPPORTED;
     }
-    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS) {
+    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS &&
+        !(algo == PDCC_ALGO_PULL && op.coll == PDCC_ALL_GATHER)) {
       set_error("algo %d is not valid for collective %d", algo, op.coll);
       return PDCC_EINVAL;
     }
@@ -199,7 +204,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   const bool oneshot_push = reduce_coll && (algo == PDCC_ALGO_ONESHOT_P2P || algo == PDCC_ALGO_P2P);
   const bool twoshot_push = reduce_coll && algo == PDCC_ALGO_TWOSHOT_P2P;
   const bool sub_slots = op.coll == PDCC_GATHER || oneshot_push ||
-                         (op.coll == PDCC_ALL_GATHER && algo == PDCC_ALGO_NVLS);
+                         (op.coll == PDCC_ALL_GATHER && algo != PDCC_ALGO_PULL);
   if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);  // one sub-slot per source rank
   if (twoshot_push) cap = comm.slot_bytes / 2;                 // partials + reduced chunks
   if (twoshot_push || (op.coll == PDCC_ALL_REDUCE && algo == PDCC_ALGO_TWOSHOT_NVLS)) {
@@ -216,7 +221,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   if (max_blocks <= 0) {
     // Bandwidth collectives: enough CTAs to keep ~4 MB in flight per GPU; the rooted
     // movers are limited by one GPU's link so fewer suffice.
-    max_blocks = 64;
+    max_blocks = 128;
   }
   if (max_blocks > ring_limit) max_blocks = ring_limit;
 
@@ -311,7 +316,9 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
       break;
     case PDCC_ALL_GATHER:
       fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll)
-           : move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_ALLGATHER_NVLS : MV_ALLGATHER_PULL);
+           : move_kernel_for(plan.algo == PDCC_ALGO_NVLS   ? MV_ALLGATHER_NVLS
+                             : plan.algo == PDCC_ALGO_PULL ? MV_ALLGATHER_PULL
+                                                           : MV_ALLGATHER_PUSH);
       break;
     case PDCC_BARRIER: fn = move_kernel_for(MV_BARRIER); break;
     default: break;

@@ -169,9 +169,10 @@ enum pdcc_algo {
   PDCC_ALGO_TWOSHOT_P2P = 2,  /* reduce-scatter + all-gather over peer pointers               */
   PDCC_ALGO_ONESHOT_NVLS = 3, /* multimem.ld_reduce of the whole tile on every rank           */
   PDCC_ALGO_TWOSHOT_NVLS = 4, /* multimem.ld_reduce own shard + multimem.st to all            */
-  PDCC_ALGO_P2P = 5,          /* rooted / gather-type collectives: peer loads/stores          */
+  PDCC_ALGO_P2P = 5,          /* rooted / gather-type collectives: posted peer stores (push)  */
   PDCC_ALGO_NVLS = 6,         /* rooted / gather-type collectives: multicast                  */
-  PDCC_ALGO_LL = 7            /* any collective, small messages: flag-in-data push, no fences */
+  PDCC_ALGO_LL = 7,           /* any collective, small messages: flag-in-data push, no fences */
+  PDCC_ALGO_PULL = 8          /* all_gather: stage own shard, read every peer's (remote loads)  */
 };
 
 typedef struct {

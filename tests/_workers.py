@@ -201,9 +201,20 @@ def native_sweep(rank, size):
                 if not torch.equal(x.cpu(), _det_input(root, count, torch.float32, seed, "cpu")):
                     failures.append(("broadcast", algo, count, root))
                 seed += 1
+                x = _det_input(rank, count, torch.float32, seed, dev)
+                keep = x.clone()
+                comm.reduce(x, root, K.SUM, algo="twoshot_p2p")
+                checked += 1
+                if rank == root:
+                    if not torch.allclose(x.cpu().double(), oracle(count, torch.float32, seed, "SUM"),
+                                          rtol=1e-5, atol=1e-5):
+                        failures.append(("reduce-2phase", count, root))
+                elif not torch.equal(x, keep):
+                    failures.append(("reduce-2phase-nonroot-touched", count, root))
+                seed += 1
                 x = _det_input(rank, count, torch.bfloat16, seed, dev)
                 lst = [torch.zeros(count, dtype=torch.bfloat16, device=dev) for _ in range(size)]
-                comm.all_gather(lst, x, algo=algo)
+                comm.all_gather(lst, x, algo="pull" if algo == "p2p" and count % 2 else algo)
                 checked += 1
                 for p in range(size):
                     if not torch.equal(lst[p].cpu(), _det_input(p, count, torch.bfloat16, seed, "cpu")):

@@ -129,7 +129,8 @@ def test_all_reduce_fused_scale_and_cast(emus):
 @pytest.mark.parametrize("n", [2, 4, 8])
 def test_reduce_leaves_non_root_untouched(emus, n):
     e = emus(n)
-    for root, algo in ((0, "p2p"), (n - 1, "p2p"), (0, "ll"), (n - 1, "ll")):
+    for root, algo in ((0, "p2p"), (n - 1, "p2p"), (0, "ll"), (n - 1, "ll"), (0, "twoshot_p2p"),
+                       (n - 1, "twoshot_p2p")):
         for op in (K.SUM, K.MAX):
             xs = _inputs(n, 33333, torch.float32, seed=root)
             before = [x.clone() for x in xs]
@@ -158,21 +159,21 @@ def test_broadcast(emus, n, dtype, algo):
 
 
 @pytest.mark.parametrize("n", [2, 4, 8])
-@pytest.mark.parametrize("algo", ["p2p", "ll"])
+@pytest.mark.parametrize("algo", ["p2p", "ll", "pull"])
 def test_scatter_gather_all_gather(emus, n, algo):
     e = emus(n)
     for count in SIZES:
         for root in (0, n // 2):
             src = _inputs(n, count, torch.float32, seed=root)  # list on the root
             outs = [torch.zeros(count, device=DEV) for _ in range(n)]
-            e.scatter(outs, src, root, algo=algo)
+            e.scatter(outs, src, root, algo=None if algo == "pull" else algo)
             e.check()
             for r in range(n):
                 assert torch.equal(outs[r], src[r])
 
             ins = _inputs(n, count, torch.float32, seed=10 + root)
             dst = [torch.zeros(count, device=DEV) for _ in range(n)]
-            e.gather(ins, dst, root, algo=algo)
+            e.gather(ins, dst, root, algo=None if algo == "pull" else algo)
             e.check()
             for r in range(n):
                 assert torch.equal(dst[r], ins[r])
