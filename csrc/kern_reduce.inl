@@ -12,7 +12,7 @@ PDCC_DECLARE_REDUCE_TABLE(PDCC_NAME) {
     case AR_ONESHOT_P2P:  return reduce_kernel<T, W, AR_ONESHOT_P2P, R>;     \
     case AR_TWOSHOT_P2P:  return reduce_kernel<T, W, AR_TWOSHOT_P2P, R>;     \
     case AR_ONESHOT_NVLS: return reduce_kernel<T, W, AR_ONESHOT_NVLS, R>;    \
-    case AR_TWOSHOT_NVLS: return R ? nullptr : reduce_kernel<T, W, AR_TWOSHOT_NVLS, false>; \
+    case AR_TWOSHOT_NVLS: return reduce_kernel<T, W, AR_TWOSHOT_NVLS, R>;    \
     case AR_LL:           return ll_reduce_kernel<T, W, R>;                  \
     default: return nullptr;                                                 \
   }

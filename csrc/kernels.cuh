@@ -409,7 +409,12 @@ struct ReducePolicy {
                 acc.scale(k.scale);
                 r = acc.pack();
               }
-              multimem_st_v4(c.mc(so) + (j << 4), r);
+              // all_reduce: the switch replicates my reduced shard into every slot.
+              // rooted reduce: only the root wants it; a plain store into the same place
+              // of ITS slot (my ld_reduce of this unit has already returned, so the
+              // operand it held there is dead).
+              if constexpr (ROOTED) st_v4(c.peer(k.root, so) + (j << 4), r);
+              else multimem_st_v4(c.mc(so) + (j << 4), r);
             } else {
               Acc<T> acc;
               acc.init(v[u]);
@@ -494,6 +499,7 @@ struct ReducePolicy {
         if (clen) copy_out(c.mine(so + size_t(k.tile_bytes) + size_t(j) * sub), off + size_t(j) * sub, clen);
       }
     } else {
+      if (ROOTED && c.rank != k.root) return;
       copy_out(c.mine(so), off, len);
     }
   }
@@ -524,6 +530,8 @@ __global__ void __launch_bounds__(kThreads, 1) reduce_kernel(const __grid_consta
 enum MoveKind : int {
   MV_BROADCAST_P2P,   // main.py:81  root stores the tile into every peer's slot
   MV_BROADCAST_NVLS,  // main.py:81  root multimem.st once, the switch replicates
+  MV_BROADCAST_2P_P2P,   // main.py:81  root scatters shards, every rank re-sends its shard
+  MV_BROADCAST_2P_NVLS,  // main.py:81  same, second phase as one multimem.st per shard
   MV_SCATTER,         // main.py:37  root pushes list[j] into rank j's slot
   MV_GATHER,          // main.py:52  rank r pushes into sub-slot r of the root's slot
   MV_ALLGATHER_PULL,  // main.py:68  stage own shard, pull every peer's into list[p]
@@ -534,7 +542,11 @@ enum MoveKind : int {
 
 template <int KIND>
 struct MovePolicy {
-  static constexpr bool kHasOut = false;
+  // Two-phase broadcast (scatter + all-gather) is the only mover with a third stage: a
+  // single GPU cannot feed n-1 peers (or the multicast engine) at link rate, n GPUs each
+  // re-sending 1/n can.
+  static constexpr bool kTwoPhase = KIND == MV_BROADCAST_2P_P2P || KIND == MV_BROADCAST_2P_NVLS;
+  static constexpr bool kHasOut = kTwoPhase;
   const KArgs& k;
   const Ctx& c;
   Geo geo;
@@ -546,13 +558,21 @@ struct MovePolicy {
   }
   static constexpr bool kRootSends = KIND == MV_BROADCAST_P2P || KIND == MV_BROADCAST_NVLS ||
                                      KIND == MV_SCATTER;
+  __device__ __forceinline__ size_t sub_bytes() const { return size_t(k.tile_bytes / c.n); }
+  __device__ __forceinline__ uint64_t chunk_len(uint64_t len, int q) const {
+    const uint64_t lo = uint64_t(q) * sub_bytes();
+    if (len <= lo) return 0;
+    return len - lo < sub_bytes() ? len - lo : sub_bytes();
+  }
   __device__ __forceinline__ uint32_t ready_to() const {
-    if constexpr (kRootSends) return c.rank == k.root ? all : 0u;
+    if constexpr (kTwoPhase) return c.rank == k.root ? all : 0u;  // root included
+    else if constexpr (kRootSends) return c.rank == k.root ? all : 0u;
     else if constexpr (KIND == MV_GATHER) return 1u << k.root;
     else return all;
   }
   __device__ __forceinline__ uint32_t ready_from() const {
-    if constexpr (kRootSends) return c.rank == k.root ? 0u : (1u << k.root);
+    if constexpr (kTwoPhase) return 1u << k.root;
+    else if constexpr (kRootSends) return c.rank == k.root ? 0u : (1u << k.root);
     else if constexpr (KIND == MV_GATHER) return c.rank == k.root ? all : 0u;
     else return all;
   }
@@ -573,6 +593,16 @@ struct MovePolicy {
       const char* src = static_cast<const char*>(c.a->in) + off;
       if constexpr (KIND == MV_BROADCAST_NVLS) push<true>(src, len, so, so, all);
       else push<false>(src, len, so, so, all & ~(1u << k.root));
+    } else if constexpr (kTwoPhase) {
+      // phase 1: shard j of the tile goes to rank j (root keeps its own in the tensor)
+      if (c.rank != k.root) return;
+      const char* src = static_cast<const char*>(c.a->in) + off;
+      const size_t sub = sub_bytes();
+      for (int i = 1; i < c.n; ++i) {
+        const int j = (c.rank + i) % c.n;
+        push<false>(src + size_t(j) * sub, chunk_len(len, j), so + size_t(j) * sub,
+                    so + size_t(j) * sub, 1u << j);
+      }
     } else if constexpr (KIND == MV_SCATTER) {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j) {
@@ -610,7 +640,22 @@ struct MovePolicy {
     const size_t so = c.slot_off(c.g0 + t);
     if constexpr (KIND == MV_BROADCAST_P2P || KIND == MV_BROADCAST_NVLS || KIND == MV_SCATTER) {
       if (c.rank == k.root) return;
-      copy_bytes<LD_SYS, 4>(static_cast<char*>(c.a->out) + off, c.mine(so), len);
+      copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + off, c.mine(so), len);
+    } else if constexpr (kTwoPhase) {
+      // phase 2: I re-send my shard to everybody who still lacks it
+      const size_t sub = sub_bytes();
+      const uint64_t clen = chunk_len(len, c.rank);
+      if (clen == 0) return;
+      const size_t mine_off = so + size_t(c.rank) * sub;
+      if (c.rank == k.root) {
+        const char* src = static_cast<const char*>(c.a->in) + off + size_t(c.rank) * sub;
+        if constexpr (KIND == MV_BROADCAST_2P_NVLS) push<true>(src, clen, mine_off, mine_off, all);
+        else push<false>(src, clen, mine_off, mine_off, all & ~(1u << c.rank));
+      } else {
+        const uint32_t others = all & ~(1u << c.rank) & ~(1u << k.root);
+        if constexpr (KIND == MV_BROADCAST_2P_NVLS) push_mc<LD_SYS, 8>(c, mine_off, c.mine(mine_off), clen);
+        else push_p2p<LD_SYS, 8>(c, mine_off, c.mine(mine_off), clen, others);
+      }
     } else if constexpr (KIND == MV_GATHER) {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j)
@@ -634,7 +679,15 @@ struct MovePolicy {
       }
     }
   }
-  __device__ __forceinline__ void out(int) {}
+  __device__ __forceinline__ void out(int t) {
+    if constexpr (kTwoPhase) {
+      if (c.rank == k.root) return;
+      uint64_t off, len;
+      geo.range(t, off, len);
+      if (len == 0) return;
+      copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + off, c.mine(c.slot_off(c.g0 + t)), len);
+    }
+  }
 };
 
 template <int KIND>

@@ -51,6 +51,8 @@ static KernelFn move_kernel_for(int kind) {
   switch (kind) {
     case MV_BROADCAST_P2P: return move_kernel<MV_BROADCAST_P2P>;
     case MV_BROADCAST_NVLS: return move_kernel<MV_BROADCAST_NVLS>;
+    case MV_BROADCAST_2P_P2P: return move_kernel<MV_BROADCAST_2P_P2P>;
+    case MV_BROADCAST_2P_NVLS: return move_kernel<MV_BROADCAST_2P_NVLS>;
     case MV_SCATTER: return move_kernel<MV_SCATTER>;
     case MV_GATHER: return move_kernel<MV_GATHER>;
     case MV_ALLGATHER_PULL: return move_kernel<MV_ALLGATHER_PULL>;
@@ -159,23 +161,36 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       // Root ingress: NVLS S (the switch reduces), one-shot push (n-1)S, two-phase push
       // (reduce-scatter among all ranks, then the owners hand their chunk to the root)
       // 2S(n-1)/n. Two-phase only pays from n = 3 and once the extra flag round is amortised.
-      if (nvls && n >= 4) algo = PDCC_ALGO_NVLS;
-      else if (n > 2 && bytes > uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 256 << 10)))
-        algo = PDCC_ALGO_TWOSHOT_P2P;
+      // A single GPU pulling everything through multimem.ld_reduce tops out near half the
+      // link rate (profiles/): large messages let every rank ld_reduce its shard and hand
+      // it to the root (two-shot), root ingress S either way.
+      const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
+      if (nvls && n >= 4) algo = bytes >= big ? PDCC_ALGO_TWOSHOT_NVLS : PDCC_ALGO_NVLS;
+      else if (n > 2 && bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
       else algo = PDCC_ALGO_P2P;
+    }
+    if (algo == PDCC_ALGO_TWOSHOT_NVLS && !nvls) {
+      set_error("NVLS reduce not available for dtype %d op %d", op.dtype, redop);
+      return PDCC_EUNSUPPORTED;
     }
     if (algo == PDCC_ALGO_NVLS && !nvls) {
       set_error("NVLS reduce not available for dtype %d op %d", op.dtype, redop);
       return PDCC_EUNSUPPORTED;
     }
-    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS && algo != PDCC_ALGO_TWOSHOT_P2P) {
+    if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS && algo != PDCC_ALGO_TWOSHOT_P2P &&
+        algo != PDCC_ALGO_TWOSHOT_NVLS) {
       set_error("algo %d is not a reduce algorithm", algo);
       return PDCC_EINVAL;
     }
   } else if (op.coll == PDCC_BROADCAST || op.coll == PDCC_ALL_GATHER) {
     if (algo == PDCC_ALGO_AUTO) {
       if (op.coll == PDCC_BROADCAST) {
-        algo = (mc_ok && n > 2) ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
+        // One GPU cannot feed the multicast engine (or n-1 peers) at link rate; from a few
+        // MB up the root scatters shards and every rank re-sends its own (two-phase).
+        const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
+        if (n <= 2) algo = PDCC_ALGO_P2P;
+        else if (bytes >= big) algo = mc_ok && n >= 4 ? PDCC_ALGO_TWOSHOT_NVLS : PDCC_ALGO_TWOSHOT_P2P;
+        else algo = mc_ok ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       } else {
         // Posted stores beat remote loads on NVLink (profiles/): push my shard into every
         // peer's slot. From n = 4 one multimem.st replaces the n-1 stores (the echo of my
@@ -183,12 +198,14 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
         algo = (mc_ok && n >= 4) ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       }
     }
-    if (algo == PDCC_ALGO_NVLS && !mc_ok) {
+    if ((algo == PDCC_ALGO_NVLS || algo == PDCC_ALGO_TWOSHOT_NVLS) && !mc_ok) {
       set_error("multicast not mapped for this comm");
       return PDCC_EUNSUPPORTED;
     }
     if (algo != PDCC_ALGO_P2P && algo != PDCC_ALGO_NVLS &&
-        !(algo == PDCC_ALGO_PULL && op.coll == PDCC_ALL_GATHER)) {
+        !(algo == PDCC_ALGO_PULL && op.coll == PDCC_ALL_GATHER) &&
+        !((algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS) &&
+          op.coll == PDCC_BROADCAST)) {
       set_error("algo %d is not valid for collective %d", algo, op.coll);
       return PDCC_EINVAL;
     }
@@ -207,7 +224,9 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
                          (op.coll == PDCC_ALL_GATHER && algo != PDCC_ALGO_PULL);
   if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);  // one sub-slot per source rank
   if (twoshot_push) cap = comm.slot_bytes / 2;                 // partials + reduced chunks
-  if (twoshot_push || (op.coll == PDCC_ALL_REDUCE && algo == PDCC_ALGO_TWOSHOT_NVLS)) {
+  const bool bcast_2p = op.coll == PDCC_BROADCAST &&
+                        (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS);
+  if (twoshot_push || bcast_2p || (reduce_coll && algo == PDCC_ALGO_TWOSHOT_NVLS)) {
     align = 16 * uint64_t(n);
     cap = cap / align * align;
   }
@@ -301,12 +320,16 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
                              plan.algo == PDCC_ALGO_LL            ? AR_LL
                              : plan.algo == PDCC_ALGO_NVLS        ? AR_ONESHOT_NVLS
                              : plan.algo == PDCC_ALGO_TWOSHOT_P2P ? AR_TWOSHOT_P2P
+                             : plan.algo == PDCC_ALGO_TWOSHOT_NVLS ? AR_TWOSHOT_NVLS
                                                                   : AR_ONESHOT_P2P,
                              true);
       break;
     case PDCC_BROADCAST:
       fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll)
-           : move_kernel_for(plan.algo == PDCC_ALGO_NVLS ? MV_BROADCAST_NVLS : MV_BROADCAST_P2P);
+           : move_kernel_for(plan.algo == PDCC_ALGO_NVLS           ? MV_BROADCAST_NVLS
+                             : plan.algo == PDCC_ALGO_TWOSHOT_NVLS ? MV_BROADCAST_2P_NVLS
+                             : plan.algo == PDCC_ALGO_TWOSHOT_P2P  ? MV_BROADCAST_2P_P2P
+                                                                   : MV_BROADCAST_P2P);
       break;
     case PDCC_SCATTER:
       fn = plan.algo == PDCC_ALGO_LL ? ll_move_kernel_for(op.coll) : move_kernel_for(MV_SCATTER);

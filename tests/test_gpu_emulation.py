@@ -145,7 +145,7 @@ def test_reduce_leaves_non_root_untouched(emus, n):
 
 @pytest.mark.parametrize("n", [2, 4, 8])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.uint8])
-@pytest.mark.parametrize("algo", ["p2p", "ll"])
+@pytest.mark.parametrize("algo", ["p2p", "ll", "twoshot_p2p"])
 def test_broadcast(emus, n, dtype, algo):
     e = emus(n)
     for count in SIZES:
