@@ -26,6 +26,10 @@
 namespace pdcc {
 
 constexpr int kThreads = 512;
+#ifndef PDCC_MIN_CTAS_PER_SM
+#define PDCC_MIN_CTAS_PER_SM 2
+#endif
+constexpr int kMinCtasPerSm = PDCC_MIN_CTAS_PER_SM;
 
 struct KArgs {
   RankArgs r;           // this rank's view (real multi-GPU launch)
@@ -37,6 +41,7 @@ struct KArgs {
   int root;
   int redop;
   float scale;
+  int stagger;  // odd CTAs run their IN stage one tile further ahead (see run_pipeline)
 };
 
 struct Geo {
@@ -99,16 +104,24 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
   // at 0 and the compare is wrap-safe, so the first DEPTH tiles pass immediately.
   auto guard = [&](uint32_t g) { wait<false>(c, CH_DONE, g - PDCC_RING_DEPTH + 1u, all); };
 
-  guard(c.g0);
-  p.in(0);
-  signal(c, CH_READY, c.g0 + 1u, p.ready_to());
+  // IN runs `la` tiles ahead of MID. All CTAs of all ranks start together, so with one
+  // fixed lookahead they would alternate between their HBM-bound and NVLink-bound stages
+  // in lockstep and leave the link idle during every local stage; odd CTAs look one tile
+  // further ahead, which skews the two halves of the grid against each other. Bounds: a
+  // slot is held until DONE, so la <= DEPTH-2 with an OUT stage and DEPTH-1 without.
+  const int la = (k.stagger && (c.b & 1)) ? 2 : 1;
+  int issued = 0;
+  auto issue_until = [&](int upto) {
+    while (issued <= upto && issued < T) {
+      guard(c.g0 + uint32_t(issued));
+      p.in(issued);
+      signal(c, CH_READY, c.g0 + uint32_t(issued) + 1u, p.ready_to());
+      ++issued;
+    }
+  };
   for (int t = 0; t < T; ++t) {
     const uint32_t g = c.g0 + uint32_t(t);
-    if (t + 1 < T) {
-      guard(g + 1u);
-      p.in(t + 1);
-      signal(c, CH_READY, g + 2u, p.ready_to());
-    }
+    issue_until(t + la);
     wait(c, CH_READY, g + 1u, p.ready_from());
     p.mid(t);
     if constexpr (P::kHasOut) {
@@ -506,7 +519,7 @@ struct ReducePolicy {
 };
 
 template <typename T, bool WIDE, int ALGO, bool ROOTED>
-__global__ void __launch_bounds__(kThreads, 1) reduce_kernel(const __grid_constant__ KArgs k) {
+__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) reduce_kernel(const __grid_constant__ KArgs k) {
   switch (k.redop) {
     case PDCC_SUM:
       run_pipeline<ReducePolicy<T, WIDE, PDCC_SUM, ALGO, ROOTED>>(k);
@@ -691,7 +704,7 @@ struct MovePolicy {
 };
 
 template <int KIND>
-__global__ void __launch_bounds__(kThreads, 1) move_kernel(const __grid_constant__ KArgs k) {
+__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) move_kernel(const __grid_constant__ KArgs k) {
   run_pipeline<MovePolicy<KIND>>(k);
 }
 

@@ -240,7 +240,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   if (max_blocks <= 0) {
     // Bandwidth collectives: enough CTAs to keep ~4 MB in flight per GPU; the rooted
     // movers are limited by one GPU's link so fewer suffice.
-    max_blocks = 128;
+    max_blocks = env_int("PDCC_DEFAULT_CTAS", 128);
   }
   if (max_blocks > ring_limit) max_blocks = ring_limit;
 
@@ -290,6 +290,7 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
   k.ntiles = plan.ntiles;
   k.root = op.root;
   k.redop = redop;
+  k.stagger = env_int("PDCC_STAGGER", 1);
   k.scale = op.scale == 0.0f ? 1.0f : op.scale;
   if (op.redop == PDCC_AVG) k.scale *= 1.0f / float(n);
 

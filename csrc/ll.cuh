@@ -168,7 +168,7 @@ __device__ __forceinline__ void run_ll(const KArgs& k) {
 }
 
 template <typename T, bool WIDE, bool ROOTED>
-__global__ void __launch_bounds__(kThreads, 1) ll_reduce_kernel(const __grid_constant__ KArgs k) {
+__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) ll_reduce_kernel(const __grid_constant__ KArgs k) {
   constexpr int KIND = ROOTED ? LL_REDUCE : LL_ALL_REDUCE;
   switch (k.redop) {
     case PDCC_SUM: run_ll<KIND, T, PDCC_SUM, WIDE>(k); break;
@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(kThreads, 1) ll_reduce_kernel(const __grid_con
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kThreads, 1) ll_move_kernel(const __grid_constant__ KArgs k) {
+__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) ll_move_kernel(const __grid_constant__ KArgs k) {
   run_ll<KIND, uint8_t, PDCC_SUM, false>(k);
 }
 

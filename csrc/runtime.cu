@@ -770,8 +770,10 @@ int pdcc_comm_check(pdcc_comm_t* c) {
   return check_block(c->dev.base[c->cfg.rank], c->cfg.rank);
 }
 
+// CTAs of one call must all be resident (they wait on their peers): 2 per SM at most.
 static int ring_limit(const pdcc_comm* c) {
-  return c->max_blocks < c->sm_count || c->sm_count <= 0 ? c->max_blocks : c->sm_count;
+  const int resident = c->sm_count > 0 ? 2 * c->sm_count : c->max_blocks;
+  return c->max_blocks < resident ? c->max_blocks : resident;
 }
 
 int pdcc_plan(pdcc_comm_t* c, const pdcc_op_t* op, int* algo, int* nblocks, int* threads,
