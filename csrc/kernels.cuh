@@ -296,12 +296,26 @@ struct ReducePolicy {
   __device__ __forceinline__ uint32_t ready_from() const {
     return (ROOTED && !kTwoShot) ? (c.rank == k.root ? all : 0u) : all;
   }
-  __device__ __forceinline__ size_t sub_bytes() const { return size_t(k.tile_bytes / c.n); }
+  // Two-shot P2P ownership. all_reduce: every rank owns one chunk of the tile. Rooted
+  // reduce: only the n-1 NON-root ranks own chunks, so the root receives each reduced
+  // chunk exactly once and nothing else: S bytes in, S bytes out on every GPU, instead of
+  // 2S(n-1)/n into the root when it also collects partials for a chunk of its own.
+  static constexpr bool kRootOwnsNothing = ROOTED && ALGO == AR_TWOSHOT_P2P;
+  __device__ __forceinline__ int nown() const { return kRootOwnsNothing ? c.n - 1 : c.n; }
+  __device__ __forceinline__ int own_index(int r) const {
+    return kRootOwnsNothing ? (r - k.root - 1 + c.n) % c.n : r;
+  }
+  __device__ __forceinline__ bool is_owner(int r) const { return !kRootOwnsNothing || r != k.root; }
+  __device__ __forceinline__ size_t sub_bytes() const { return size_t(k.tile_bytes / nown()); }
   // bytes of chunk q inside a tile of `len` valid bytes
   __device__ __forceinline__ uint64_t chunk_len(uint64_t len, int q) const {
     const uint64_t lo = uint64_t(q) * sub_bytes();
     if (len <= lo) return 0;
     return len - lo < sub_bytes() ? len - lo : sub_bytes();
+  }
+  // A[p] (partials from rank p) sits at p*sub, B[o] (reduced chunk o) behind the n A's
+  __device__ __forceinline__ size_t b_off(size_t so, int o) const {
+    return so + (size_t(c.n) + size_t(o)) * sub_bytes();
   }
 
   __device__ __forceinline__ void in(int t) {
@@ -319,12 +333,14 @@ struct ReducePolicy {
       } else {
         push_user<false>(c, src, len, mine_off, mine_off, all & ~(1u << c.rank));
       }
-    } else {  // two-shot P2P: my partial of chunk p goes to its owner p
+    } else {  // two-shot P2P: my partial of each chunk goes to the chunk's owner
       const size_t sub = sub_bytes();
       for (int i = 1; i < c.n; ++i) {
         const int p = (c.rank + i) % c.n;
-        push_user<false>(c, src + size_t(p) * sub, chunk_len(len, p), so + size_t(c.rank) * sub,
-                         so + k.tile_bytes + size_t(p) * sub, 1u << p);
+        if (!is_owner(p)) continue;
+        const int o = own_index(p);
+        push_user<false>(c, src + size_t(o) * sub, chunk_len(len, o), so + size_t(c.rank) * sub,
+                         b_off(so, o), 1u << p);
       }
     }
   }
@@ -458,17 +474,17 @@ struct ReducePolicy {
       if (ROOTED && c.rank != k.root) return;
       mid_nvls<false>(so, 0, n16, nelem, elem0);
     } else if constexpr (ALGO == AR_TWOSHOT_P2P) {
-      // I own chunk `me` of the tile: combine the partials in A, write my part of the
-      // result and hand the reduced chunk to everyone who needs it (B[me] on their side).
+      // I own one chunk of the tile: combine the partials in A, keep my part of the result
+      // (all_reduce) and hand the reduced chunk to whoever needs it (B[o] on their side).
+      if (!is_owner(c.rank)) return;
+      const int o = own_index(c.rank);
       const size_t sub = sub_bytes();
-      const uint64_t clen = chunk_len(len, c.rank);
+      const uint64_t clen = chunk_len(len, o);
       if (clen == 0) return;
       const uint32_t others = all & ~(1u << c.rank);
-      const uint32_t push_mask = ROOTED ? (c.rank == k.root ? 0u : (1u << k.root)) : others;
-      const bool write_out = !ROOTED || c.rank == k.root;
-      combine_dispatch(src + size_t(c.rank) * sub, clen, so, sub, size_t((clen + 15) >> 4),
-                       elem0 + size_t(c.rank) * sub / sizeof(T), write_out,
-                       so + size_t(k.tile_bytes) + size_t(c.rank) * sub, push_mask);
+      const uint32_t push_mask = ROOTED ? (1u << k.root) : others;
+      combine_dispatch(src + size_t(o) * sub, clen, so, sub, size_t((clen + 15) >> 4),
+                       elem0 + size_t(o) * sub / sizeof(T), !ROOTED, b_off(so, o), push_mask);
     } else {
       // NVLS two-shot: this rank owns units [lo, hi) of the tile
       const size_t sub16 = (k.tile_bytes / c.n) >> 4;
@@ -507,9 +523,10 @@ struct ReducePolicy {
       if (ROOTED && c.rank != k.root) return;
       const size_t sub = sub_bytes();
       for (int i = 1; i < c.n; ++i) {
-        const int j = (c.rank + i) % c.n;
-        const uint64_t clen = chunk_len(len, j);
-        if (clen) copy_out(c.mine(so + size_t(k.tile_bytes) + size_t(j) * sub), off + size_t(j) * sub, clen);
+        const int j = (c.rank + i) % c.n;  // every owner but me
+        const int o = own_index(j);
+        const uint64_t clen = chunk_len(len, o);
+        if (clen) copy_out(c.mine(b_off(so, o)), off + size_t(o) * sub, clen);
       }
     } else {
       if (ROOTED && c.rank != k.root) return;
@@ -571,7 +588,9 @@ struct MovePolicy {
   }
   static constexpr bool kRootSends = KIND == MV_BROADCAST_P2P || KIND == MV_BROADCAST_NVLS ||
                                      KIND == MV_SCATTER;
-  __device__ __forceinline__ size_t sub_bytes() const { return size_t(k.tile_bytes / c.n); }
+  // two-phase broadcast: the n-1 non-root ranks each own one shard of the tile
+  __device__ __forceinline__ int own_index(int r) const { return (r - k.root - 1 + c.n) % c.n; }
+  __device__ __forceinline__ size_t sub_bytes() const { return size_t(k.tile_bytes / (c.n - 1)); }
   __device__ __forceinline__ uint64_t chunk_len(uint64_t len, int q) const {
     const uint64_t lo = uint64_t(q) * sub_bytes();
     if (len <= lo) return 0;
@@ -607,14 +626,15 @@ struct MovePolicy {
       if constexpr (KIND == MV_BROADCAST_NVLS) push<true>(src, len, so, so, all);
       else push<false>(src, len, so, so, all & ~(1u << k.root));
     } else if constexpr (kTwoPhase) {
-      // phase 1: shard j of the tile goes to rank j (root keeps its own in the tensor)
+      // phase 1: the root deals one shard of the tile to each other rank (S bytes out)
       if (c.rank != k.root) return;
       const char* src = static_cast<const char*>(c.a->in) + off;
       const size_t sub = sub_bytes();
       for (int i = 1; i < c.n; ++i) {
         const int j = (c.rank + i) % c.n;
-        push<false>(src + size_t(j) * sub, chunk_len(len, j), so + size_t(j) * sub,
-                    so + size_t(j) * sub, 1u << j);
+        const int o = own_index(j);
+        push<false>(src + size_t(o) * sub, chunk_len(len, o), so + size_t(o) * sub,
+                    so + size_t(o) * sub, 1u << j);
       }
     } else if constexpr (KIND == MV_SCATTER) {
       if (c.rank != k.root) return;
@@ -655,20 +675,17 @@ struct MovePolicy {
       if (c.rank == k.root) return;
       copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + off, c.mine(so), len);
     } else if constexpr (kTwoPhase) {
-      // phase 2: I re-send my shard to everybody who still lacks it
+      // phase 2: every non-root rank re-sends its shard to the other non-root ranks, so
+      // each of them also receives exactly S bytes and sends at most S.
+      if (c.rank == k.root) return;
       const size_t sub = sub_bytes();
-      const uint64_t clen = chunk_len(len, c.rank);
+      const int o = own_index(c.rank);
+      const uint64_t clen = chunk_len(len, o);
       if (clen == 0) return;
-      const size_t mine_off = so + size_t(c.rank) * sub;
-      if (c.rank == k.root) {
-        const char* src = static_cast<const char*>(c.a->in) + off + size_t(c.rank) * sub;
-        if constexpr (KIND == MV_BROADCAST_2P_NVLS) push<true>(src, clen, mine_off, mine_off, all);
-        else push<false>(src, clen, mine_off, mine_off, all & ~(1u << c.rank));
-      } else {
-        const uint32_t others = all & ~(1u << c.rank) & ~(1u << k.root);
-        if constexpr (KIND == MV_BROADCAST_2P_NVLS) push_mc<LD_SYS, 8>(c, mine_off, c.mine(mine_off), clen);
-        else push_p2p<LD_SYS, 8>(c, mine_off, c.mine(mine_off), clen, others);
-      }
+      const size_t mine_off = so + size_t(o) * sub;
+      const uint32_t others = all & ~(1u << c.rank) & ~(1u << k.root);
+      if constexpr (KIND == MV_BROADCAST_2P_NVLS) push_mc<LD_SYS, 8>(c, mine_off, c.mine(mine_off), clen);
+      else push_p2p<LD_SYS, 8>(c, mine_off, c.mine(mine_off), clen, others);
     } else if constexpr (KIND == MV_GATHER) {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j)

@@ -141,7 +141,8 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       } else if (bytes <= uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 1 << 20))) {
         algo = PDCC_ALGO_ONESHOT_P2P;
       } else {
-        algo = (nvls && n >= 4) ? PDCC_ALGO_TWOSHOT_NVLS : PDCC_ALGO_TWOSHOT_P2P;
+        algo = (nvls && n > env_int("PDCC_NVLS_MIN_RANKS", 4)) ? PDCC_ALGO_TWOSHOT_NVLS
+                                                               : PDCC_ALGO_TWOSHOT_P2P;
       }
     }
     if ((algo == PDCC_ALGO_ONESHOT_NVLS || algo == PDCC_ALGO_TWOSHOT_NVLS) && !nvls) {
@@ -162,11 +163,11 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       // (reduce-scatter among all ranks, then the owners hand their chunk to the root)
       // 2S(n-1)/n. Two-phase only pays from n = 3 and once the extra flag round is amortised.
       // A single GPU pulling everything through multimem.ld_reduce tops out near half the
-      // link rate (profiles/): large messages let every rank ld_reduce its shard and hand
-      // it to the root (two-shot), root ingress S either way.
+      // link rate (profiles/). Large messages: two-shot push where only the non-root ranks
+      // own chunks: S bytes in and out of every GPU, all of it posted stores.
       const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
-      if (nvls && n >= 4) algo = bytes >= big ? PDCC_ALGO_TWOSHOT_NVLS : PDCC_ALGO_NVLS;
-      else if (n > 2 && bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
+      if (n > 2 && bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
+      else if (nvls && n >= 4) algo = PDCC_ALGO_NVLS;
       else algo = PDCC_ALGO_P2P;
     }
     if (algo == PDCC_ALGO_TWOSHOT_NVLS && !nvls) {
@@ -186,10 +187,11 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
     if (algo == PDCC_ALGO_AUTO) {
       if (op.coll == PDCC_BROADCAST) {
         // One GPU cannot feed the multicast engine (or n-1 peers) at link rate; from a few
-        // MB up the root scatters shards and every rank re-sends its own (two-phase).
+        // MB up the root deals shards to the other ranks and they re-send them among
+        // themselves (two-phase, unicast stores, S bytes per GPU and direction).
         const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
         if (n <= 2) algo = PDCC_ALGO_P2P;
-        else if (bytes >= big) algo = mc_ok && n >= 4 ? PDCC_ALGO_TWOSHOT_NVLS : PDCC_ALGO_TWOSHOT_P2P;
+        else if (bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
         else algo = mc_ok ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       } else {
         // Posted stores beat remote loads on NVLink (profiles/): push my shard into every
@@ -213,6 +215,11 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
     algo = PDCC_ALGO_P2P;
   }
 
+  // the root-owns-nothing two-phase variants need at least one other rank to own chunks
+  if (n < 2 && (op.coll == PDCC_REDUCE || op.coll == PDCC_BROADCAST) &&
+      (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS))
+    algo = PDCC_ALGO_P2P;
+
   // ---- grid + tile ---------------------------------------------------------------
   // cap: payload one CTA may place in one slot for this collective
   uint64_t cap = comm.slot_bytes;
@@ -223,11 +230,15 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   const bool sub_slots = op.coll == PDCC_GATHER || oneshot_push ||
                          (op.coll == PDCC_ALL_GATHER && algo != PDCC_ALGO_PULL);
   if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);  // one sub-slot per source rank
-  if (twoshot_push) cap = comm.slot_bytes / 2;                 // partials + reduced chunks
   const bool bcast_2p = op.coll == PDCC_BROADCAST &&
                         (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS);
+  // chunk owners: every rank, or every rank but the root (rooted two-shot push, two-phase
+  // broadcast), see ReducePolicy / MovePolicy
+  const uint64_t nown = ((twoshot_push && op.coll == PDCC_REDUCE) || bcast_2p) ? uint64_t(n - 1)
+                                                                               : uint64_t(n);
+  if (twoshot_push) cap = comm.slot_bytes * nown / (uint64_t(n) + nown);  // n partials + reduced chunks
   if (twoshot_push || bcast_2p || (reduce_coll && algo == PDCC_ALGO_TWOSHOT_NVLS)) {
-    align = 16 * uint64_t(n);
+    align = 16 * (nown ? nown : 1);
     cap = cap / align * align;
   }
   if (cap < align) {
@@ -240,7 +251,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   if (max_blocks <= 0) {
     // Bandwidth collectives: enough CTAs to keep ~4 MB in flight per GPU; the rooted
     // movers are limited by one GPU's link so fewer suffice.
-    max_blocks = env_int("PDCC_DEFAULT_CTAS", 128);
+    max_blocks = env_int("PDCC_DEFAULT_CTAS", 256);
   }
   if (max_blocks > ring_limit) max_blocks = ring_limit;
 
