@@ -155,6 +155,10 @@ struct Ctx {
   uint32_t* ctrl;
   uint64_t deadline;  // globaltimer value after which waits give up
   int* poisoned;      // smem: a wait already timed out in this CTA
+  // The team this thread currently works in. Stage code strides its loops by (tid, nt) and
+  // synchronises on named barrier `bar`; run_pipeline() splits the CTA into two teams so
+  // that the push of tile t+1 and the combine/copy-out of tile t run at the same time.
+  int tid, nt, bar;
 
   __device__ __forceinline__ size_t slot_off(uint32_t g) const {
     return kDataOffset +
@@ -167,6 +171,10 @@ struct Ctx {
   __device__ __forceinline__ char* mine(size_t off) const { return a->comm.base[rank] + off; }
   __device__ __forceinline__ char* mc(size_t off) const { return a->comm.mc + off; }
 };
+
+__device__ __forceinline__ void team_sync(const Ctx& c) {
+  asm volatile("bar.sync %0, %1;" ::"r"(c.bar), "r"(c.nt) : "memory");
+}
 
 __device__ __forceinline__ int flag_index(int chan, int b, int src) {
   return (chan * PDCC_MAX_BLOCKS + b) * PDCC_MAX_RANKS + src;
@@ -195,6 +203,31 @@ __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
 __device__ __forceinline__ void signal_relaxed(const Ctx& c, int chan, uint32_t val,
                                                uint32_t mask) {
   __syncthreads();
+  const int t = threadIdx.x;
+  if (t < c.n && ((mask >> t) & 1u)) {
+    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
+    st_relaxed_sys(pad + flag_index(chan, c.b, c.rank), val);
+  }
+}
+
+// Building blocks of the fused per-tile flag round in run_pipeline(): thread t (< nranks)
+// polls / posts rank t's flag; fences and CTA barriers are the caller's.
+__device__ __forceinline__ void spin_flag(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+  const int t = threadIdx.x;
+  if (t < c.n && ((mask >> t) & 1u) && !*c.poisoned) {
+    const uint32_t* f = c.my_pad + flag_index(chan, c.b, t);
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_relaxed_sys(f) - val) < 0) {
+      if ((++spins & 0x3ffu) == 0 && globaltimer_ns() > c.deadline) {
+        if (atomicCAS(c.ctrl + kCtrlErr, 0u, 1u) == 0u)
+          c.ctrl[kCtrlErrInfo] = (uint32_t(chan) << 28) | (uint32_t(t) << 24) | (val & 0xffffffu);
+        *c.poisoned = 1;
+        break;
+      }
+    }
+  }
+}
+__device__ __forceinline__ void post_flag(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
   const int t = threadIdx.x;
   if (t < c.n && ((mask >> t) & 1u)) {
     uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
@@ -251,8 +284,8 @@ __device__ __forceinline__ bool aligned16(const void* p) {
 
 // 16-byte vector copy of n16 units, UNROLL independent loads in flight per thread.
 template <int UNROLL>
-__device__ __noinline__ void copy16(char* __restrict__ d, const char* __restrict__ s, size_t n16) {
-  const int tid = threadIdx.x, nt = blockDim.x;
+__device__ __noinline__ void copy16(char* __restrict__ d, const char* __restrict__ s, size_t n16,
+                                    int tid, int nt) {
   const size_t pass = size_t(nt) * UNROLL;
   const size_t nmain = n16 / pass * pass;
   for (size_t i = tid; i < nmain; i += pass) {
@@ -268,13 +301,13 @@ __device__ __noinline__ void copy16(char* __restrict__ d, const char* __restrict
 // CTA-wide copy of n bytes. Fast path: both sides 16-byte aligned. Anything else degrades
 // to 4- or 1-byte words; that only happens for odd user views (slot addresses are aligned).
 template <int LD, int UNROLL>
-__device__ __forceinline__ void copy_bytes(void* dst, const void* src, size_t n) {
-  const int tid = threadIdx.x, nt = blockDim.x;
+__device__ __forceinline__ void copy_bytes(const Ctx& c, void* dst, const void* src, size_t n) {
+  const int tid = c.tid, nt = c.nt;
   char* d = static_cast<char*>(dst);
   const char* s = static_cast<const char*>(src);
   if (aligned16(d) && aligned16(s)) {
     const size_t n16 = n >> 4;
-    copy16<UNROLL>(d, s, n16);
+    copy16<UNROLL>(d, s, n16, tid, nt);
     for (size_t i = (n16 << 4) + tid; i < n; i += nt) d[i] = s[i];
   } else if (((reinterpret_cast<uintptr_t>(d) | reinterpret_cast<uintptr_t>(s)) & 3u) == 0) {
     const size_t n4 = n >> 2;
@@ -291,8 +324,8 @@ __device__ __forceinline__ void copy_bytes(void* dst, const void* src, size_t n)
 // rank in `mask` (P2P stores). n is rounded up to 16 (slots have room).
 template <int UNROLL>
 __device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nranks, uint32_t mask,
-                                        size_t off, const char* __restrict__ s, size_t n16) {
-  const int tid = threadIdx.x, nt = blockDim.x;
+                                        size_t off, const char* __restrict__ s, size_t n16,
+                                        int tid, int nt) {
   if (mask == 0) return;  // a group of one has nobody to push to
   if ((mask & (mask - 1u)) == 0) {  // one target: scatter, gather, reduce-scatter phase
     char* d = base[__ffs(int(mask)) - 1] + off;
@@ -334,14 +367,14 @@ __device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nran
 template <int LD, int UNROLL>
 __device__ __forceinline__ void push_p2p(const Ctx& c, size_t off, const void* src, size_t n,
                                          uint32_t mask) {
-  push16_p2p<UNROLL>(c.a->comm.base, c.n, mask, off, static_cast<const char*>(src), (n + 15) >> 4);
+  push16_p2p<UNROLL>(c.a->comm.base, c.n, mask, off, static_cast<const char*>(src), (n + 15) >> 4,
+                     c.tid, c.nt);
 }
 
 // Same through the multicast alias: one multimem.st per 16 bytes reaches every rank.
 template <int UNROLL>
 __device__ __noinline__ void push16_mc(char* __restrict__ d, const char* __restrict__ s,
-                                       size_t n16) {
-  const int tid = threadIdx.x, nt = blockDim.x;
+                                       size_t n16, int tid, int nt) {
   const size_t pass = size_t(nt) * UNROLL;
   const size_t nmain = n16 / pass * pass;
   for (size_t i = tid; i < nmain; i += pass) {
@@ -357,7 +390,7 @@ __device__ __noinline__ void push16_mc(char* __restrict__ d, const char* __restr
 
 template <int LD, int UNROLL>
 __device__ __forceinline__ void push_mc(const Ctx& c, size_t off, const void* src, size_t n) {
-  push16_mc<UNROLL>(c.mc(off), static_cast<const char*>(src), (n + 15) >> 4);
+  push16_mc<UNROLL>(c.mc(off), static_cast<const char*>(src), (n + 15) >> 4, c.tid, c.nt);
 }
 
 }  // namespace pdcc

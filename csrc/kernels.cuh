@@ -27,7 +27,7 @@ namespace pdcc {
 
 constexpr int kThreads = 512;
 #ifndef PDCC_MIN_CTAS_PER_SM
-#define PDCC_MIN_CTAS_PER_SM 2
+#define PDCC_MIN_CTAS_PER_SM 1
 #endif
 constexpr int kMinCtasPerSm = PDCC_MIN_CTAS_PER_SM;
 
@@ -78,6 +78,9 @@ __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
   c.rank = a->comm.rank;
   c.n = a->comm.nranks;
   c.b = blockIdx.x;
+  c.tid = threadIdx.x;
+  c.nt = blockDim.x;
+  c.bar = 0;
   c.my_pad = reinterpret_cast<uint32_t*>(a->comm.base[c.rank] + kCtrlBytes);
   c.ctrl = reinterpret_cast<uint32_t*>(a->comm.base[c.rank]);
   c.poisoned = &sh.poison;
@@ -90,6 +93,16 @@ __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
   c.g0 = sh.g0;
 }
 
+// One flag round per tile. Iteration t
+//   (1) waits for everything it is about to consume: the slot of tile t+1 being free
+//       (DONE of tile t+1-DEPTH), READY(t), and MID(t-1) when there is an OUT stage;
+//   (2) runs IN(t+1), MID(t) and OUT(t-1) AT THE SAME TIME on two teams of warps — the push
+//       of the next tile (NVLink egress, or a local copy-in) overlaps the combine / re-send
+//       / copy-out of the current one, so the stages that load different links (or HBM)
+//       never idle each other, even when all CTAs of all ranks run in lockstep;
+//   (3) publishes READY(t+1), MID(t) and DONE with ONE system fence.
+// A rank that has only one kind of work in a collective (the root of a scatter only pushes,
+// the others only copy out) keeps all its threads on it.
 template <class P>
 __device__ __forceinline__ void run_pipeline(const KArgs& k) {
   __shared__ Prologue sh;
@@ -99,46 +112,79 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
   const uint32_t all = (1u << c.n) - 1u;
   const int T = k.ntiles;
   P p(k, c);
-
-  // Ring position of tile g is free once every rank finished tile g - DEPTH. Flags start
-  // at 0 and the compare is wrap-safe, so the first DEPTH tiles pass immediately.
-  auto guard = [&](uint32_t g) { wait<false>(c, CH_DONE, g - PDCC_RING_DEPTH + 1u, all); };
-
-  // IN runs `la` tiles ahead of MID. All CTAs of all ranks start together, so with one
-  // fixed lookahead they would alternate between their HBM-bound and NVLink-bound stages
-  // in lockstep and leave the link idle during every local stage; odd CTAs look one tile
-  // further ahead, which skews the two halves of the grid against each other. Bounds: a
-  // slot is held until DONE, so la <= DEPTH-2 with an OUT stage and DEPTH-1 without.
-  const int la = (k.stagger && (c.b & 1)) ? 2 : 1;
-  int issued = 0;
-  auto issue_until = [&](int upto) {
-    while (issued <= upto && issued < T) {
-      guard(c.g0 + uint32_t(issued));
-      p.in(issued);
-      signal(c, CH_READY, c.g0 + uint32_t(issued) + 1u, p.ready_to());
-      ++issued;
-    }
+  const int half = int(blockDim.x) >> 1;
+  const bool team_a = int(threadIdx.x) < half;
+  const bool flag_thread = int(threadIdx.x) < c.n;
+  auto whole = [&] { c.tid = threadIdx.x; c.nt = blockDim.x; c.bar = 0; };
+  auto split = [&] {
+    c.nt = half;
+    c.tid = team_a ? int(threadIdx.x) : int(threadIdx.x) - half;
+    c.bar = team_a ? 1 : 2;
   };
+  const bool has_in = p.has_in(), has_mid = p.has_mid(), has_out = P::kHasOut && p.has_out();
+
+  // prologue: tile 0 enters the pipeline. Flags start at 0 and the compare is wrap-safe,
+  // so the first DEPTH tiles of a ring pass the slot guard immediately.
+  spin_flag(c, CH_DONE, c.g0 - PDCC_RING_DEPTH + 1u, all);
+  __syncthreads();
+  if (has_in) p.in(0);
+  __syncthreads();
+  if (flag_thread) {
+    fence_acq_rel_sys();
+    post_flag(c, CH_READY, c.g0 + 1u, p.ready_to());
+  }
+
   for (int t = 0; t < T; ++t) {
     const uint32_t g = c.g0 + uint32_t(t);
-    issue_until(t + la);
-    wait(c, CH_READY, g + 1u, p.ready_from());
-    p.mid(t);
-    if constexpr (P::kHasOut) {
-      signal(c, CH_MID, g + 1u, all);
-      if (t >= 1) {
-        wait(c, CH_MID, g, all);
-        p.out(t - 1);
-        signal_relaxed(c, CH_DONE, g, all);
+    const bool more = t + 1 < T;
+    // (1)
+    if (more) spin_flag(c, CH_DONE, g + 1u - PDCC_RING_DEPTH + 1u, all);
+    spin_flag(c, CH_READY, g + 1u, p.ready_from());
+    if (P::kHasOut && t >= 1) spin_flag(c, CH_MID, g, all);
+    if (flag_thread) fence_acq_rel_sys();
+    __syncthreads();
+    // (2)
+    const bool do_in = more && has_in, do_out = has_out && t >= 1;
+    const int jobs = int(do_in) + int(has_mid) + int(do_out);
+    if (jobs >= 2) {
+      split();
+      if (do_in) {  // team A pushes the next tile, team B finishes the current ones
+        if (team_a) {
+          p.in(t + 1);
+        } else {
+          if (has_mid) p.mid(t);
+          if (do_out) p.out(t - 1);
+        }
+      } else {  // no IN on this rank: re-send and copy-out side by side
+        if (team_a) p.out(t - 1);
+        else p.mid(t);
       }
+      whole();
     } else {
-      signal_relaxed(c, CH_DONE, g + 1u, all);
+      if (do_in) p.in(t + 1);
+      if (has_mid) p.mid(t);
+      if (do_out) p.out(t - 1);
+    }
+    // (3)
+    __syncthreads();
+    if (flag_thread) {
+      fence_acq_rel_sys();
+      if (more) post_flag(c, CH_READY, g + 2u, p.ready_to());
+      if constexpr (P::kHasOut) {
+        post_flag(c, CH_MID, g + 1u, all);
+        if (t >= 1) post_flag(c, CH_DONE, g, all);
+      } else {
+        post_flag(c, CH_DONE, g + 1u, all);
+      }
     }
   }
   if constexpr (P::kHasOut) {
-    wait(c, CH_MID, c.g0 + uint32_t(T), all);
-    p.out(T - 1);
-    signal_relaxed(c, CH_DONE, c.g0 + uint32_t(T), all);
+    spin_flag(c, CH_MID, c.g0 + uint32_t(T), all);
+    if (flag_thread) fence_acq_rel_sys();
+    __syncthreads();
+    if (has_out) p.out(T - 1);
+    __syncthreads();
+    post_flag(c, CH_DONE, c.g0 + uint32_t(T), all);
   }
   if (threadIdx.x == 0) c.ctrl[kCtrlEpoch + c.b] = c.g0 + uint32_t(T);
 }
@@ -192,11 +238,11 @@ __device__ __forceinline__ void push_user(const Ctx& c, const char* src, uint64_
     if constexpr (MC) push_mc<LD_USER, 8>(c, dst_off, src, len);
     else push_p2p<LD_USER, 8>(c, dst_off, src, len, mask);
   } else {
-    copy_bytes<LD_USER, 4>(c.mine(stage_off), src, len);
-    __syncthreads();
+    copy_bytes<LD_USER, 4>(c, c.mine(stage_off), src, len);
+    team_sync(c);
     if constexpr (MC) push_mc<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len);
     else push_p2p<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len, mask);
-    __syncthreads();
+    team_sync(c);
   }
 }
 
@@ -211,9 +257,8 @@ __device__ __noinline__ void combine_main(const char* __restrict__ user,
                                           const char* __restrict__ slot_a, size_t a_stride,
                                           size_t nmain, void* __restrict__ out, float scale,
                                           int rank, int n, char* const* __restrict__ base,
-                                          size_t b_off, uint32_t push_mask) {
+                                          size_t b_off, uint32_t push_mask, int tid, int nt) {
   using Tr = Traits<T>;
-  const int tid = threadIdx.x, nt = blockDim.x;
   const size_t pass = size_t(nt) * U;
   const bool scaled = scale != 1.0f;
   for (size_t j0 = tid; j0 < nmain; j0 += pass) {
@@ -262,6 +307,55 @@ __device__ __noinline__ void combine_main(const char* __restrict__ user,
   }
 }
 
+// Hot loop of the NVLS reductions over units [lo, hi) of a slot: 8 multimem.ld_reduce in
+// flight per thread, then either the replicated store (all_reduce two-shot), a plain store
+// into the root's slot (rooted two-shot) or the vector store to the user tensor (one-shot).
+template <typename T, int KMM, bool TWOSHOT, bool ROOTED, bool WIDE>
+__device__ __noinline__ void nvls_units(char* __restrict__ mc, char* __restrict__ root_slot,
+                                        void* __restrict__ out, size_t lo, size_t hi, float scale,
+                                        int tid, int nt) {
+  using Tr = Traits<T>;
+  constexpr int U = 8;
+  const bool scaled = scale != 1.0f;
+  for (size_t j0 = lo + tid; j0 < hi; j0 += size_t(nt) * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = j0 + size_t(u) * nt;
+      v[u] = multimem_ld_reduce_v4<KMM>(mc + ((j < hi ? j : j0) << 4));
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t j = j0 + size_t(u) * nt;
+      if (j < hi) {
+        uint4 r = v[u];
+        Acc<T> acc;
+        if (scaled || (!TWOSHOT && WIDE)) {
+          acc.init(r);
+          if (scaled) acc.scale(scale);
+          r = acc.pack();
+        }
+        if constexpr (TWOSHOT) {
+          if constexpr (ROOTED) st_v4(root_slot + (j << 4), r);
+          else multimem_st_v4(mc + (j << 4), r);
+        } else if constexpr (WIDE) {
+          float* o = static_cast<float*>(out) + j * Tr::K;
+#pragma unroll
+          for (int i = 0; i < Tr::K; i += 4) {
+            uint4 w;
+            float* f = reinterpret_cast<float*>(&w);
+            f[0] = float(acc.v[i]); f[1] = float(acc.v[i + 1]);
+            f[2] = float(acc.v[i + 2]); f[3] = float(acc.v[i + 3]);
+            st_v4(o + i, w);
+          }
+        } else {
+          st_v4(static_cast<T*>(out) + j * Tr::K, r);
+        }
+      }
+    }
+  }
+}
+
 // Slot layouts (offsets from the tile's slot, `tile` = KArgs::tile_bytes, `sub` = tile/n):
 //   one-shot P2P  A[q] at q*stride            rank q's whole tile        (tile <= slot/n)
 //   two-shot P2P  A[q] at q*sub               rank q's partial of MY chunk
@@ -296,6 +390,17 @@ struct ReducePolicy {
   __device__ __forceinline__ uint32_t ready_from() const {
     return (ROOTED && !kTwoShot) ? (c.rank == k.root ? all : 0u) : all;
   }
+  // which stages have work on THIS rank (uniform across the CTA)
+  __device__ __forceinline__ bool has_in() const {
+    return !(ROOTED && ALGO == AR_ONESHOT_P2P && c.rank == k.root);
+  }
+  __device__ __forceinline__ bool has_mid() const {
+    if constexpr (!ROOTED) return true;
+    else if constexpr (ALGO == AR_TWOSHOT_P2P) return c.rank != k.root;  // owners
+    else if constexpr (ALGO == AR_TWOSHOT_NVLS) return true;
+    else return c.rank == k.root;
+  }
+  __device__ __forceinline__ bool has_out() const { return !ROOTED || c.rank == k.root; }
   // Two-shot P2P ownership. all_reduce: every rank owns one chunk of the tile. Rooted
   // reduce: only the n-1 NON-root ranks own chunks, so the root receives each reduced
   // chunk exactly once and nothing else: S bytes in, S bytes out on every GPU, instead of
@@ -325,7 +430,7 @@ struct ReducePolicy {
     const size_t so = c.slot_off(c.g0 + t);
     const char* src = static_cast<const char*>(c.a->in) + off;
     if constexpr (kNvls) {
-      copy_bytes<LD_USER, 8>(c.mine(so), src, len);
+      copy_bytes<LD_USER, 8>(c, c.mine(so), src, len);
     } else if constexpr (ALGO == AR_ONESHOT_P2P) {
       const size_t mine_off = so + size_t(c.rank) * k.stride;
       if constexpr (ROOTED) {
@@ -357,7 +462,7 @@ struct ReducePolicy {
   __device__ __forceinline__ void combine_units(const char* user, uint64_t user_len, size_t a_off,
                                                 size_t a_stride, size_t nunits, size_t elem0,
                                                 bool write_out, size_t b_off, uint32_t push_mask) {
-    const int tid = threadIdx.x, nt = blockDim.x;
+    const int tid = c.tid, nt = c.nt;
     const bool scaled = k.scale != 1.0f;
     const size_t nelem = user_len / sizeof(T);
     using Out = typename std::conditional<WIDE, float, T>::type;
@@ -376,7 +481,7 @@ struct ReducePolicy {
       combine_main<T, OP, WIDE, kTwoShot, NP, U>(user, slot_a, a_stride, nmain,
                                                  write_out ? static_cast<void*>(outp) : nullptr,
                                                  k.scale, c.rank, c.n, c.a->comm.base, b_off,
-                                                 push_mask);
+                                                 push_mask, tid, nt);
 
     // remainder, ragged tail, odd views: one unit per thread per pass, byte-exact on the
     // user side (load_user_unit / store_unit take their vector path when they can)
@@ -411,48 +516,33 @@ struct ReducePolicy {
     else combine_units<8, 1>(a...);
   }
 
-  // NVLS: the switch reduces; 8 multimem.ld_reduce in flight per thread.
+  // NVLS: the switch reduces (nvls_units, below the class).
   template <bool TWOSHOT>
   __device__ __forceinline__ void mid_nvls(size_t so, size_t lo, size_t hi, size_t nelem,
                                            size_t elem0) {
     if constexpr (kMm != MM_NONE) {
-      constexpr int U = 8;
-      const int tid = threadIdx.x, nt = blockDim.x;
-      const bool scaled = k.scale != 1.0f;
-      for (size_t j0 = lo + tid; j0 < hi; j0 += size_t(nt) * U) {
-        uint4 v[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const size_t j = j0 + size_t(u) * nt;
-          if (j < hi) v[u] = multimem_ld_reduce_v4<kMm>(c.mc(so) + (j << 4));
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const size_t j = j0 + size_t(u) * nt;
-          if (j < hi) {
-            if constexpr (TWOSHOT) {
-              uint4 r = v[u];
-              if (scaled) {
-                Acc<T> acc;
-                acc.init(r);
-                acc.scale(k.scale);
-                r = acc.pack();
-              }
-              // all_reduce: the switch replicates my reduced shard into every slot.
-              // rooted reduce: only the root wants it; a plain store into the same place
-              // of ITS slot (my ld_reduce of this unit has already returned, so the
-              // operand it held there is dead).
-              if constexpr (ROOTED) st_v4(c.peer(k.root, so) + (j << 4), r);
-              else multimem_st_v4(c.mc(so) + (j << 4), r);
-            } else {
-              Acc<T> acc;
-              acc.init(v[u]);
-              if (scaled) acc.scale(k.scale);
-              const size_t e = j * Tr::K;
-              const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
-              store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
-            }
-          }
+      using Out = typename std::conditional<WIDE, float, T>::type;
+      Out* outp = static_cast<Out*>(c.a->out) + elem0;
+      // full, aligned units go through the unrolled loop; the ragged last unit (one-shot
+      // only: two-shot works on whole units of the slot) through the scalar-safe path
+      const bool vec_out = TWOSHOT || aligned16(outp);
+      size_t hi_main = hi;
+      if (!TWOSHOT) {
+        const size_t full = nelem / Tr::K;  // units that are entirely inside the tensor
+        hi_main = vec_out ? (full < hi ? full : hi) : lo;
+        if (hi_main < lo) hi_main = lo;
+      }
+      nvls_units<T, kMm, TWOSHOT, ROOTED, WIDE>(
+          c.mc(so), ROOTED && TWOSHOT ? c.peer(k.root, so) : nullptr, outp, lo, hi_main, k.scale,
+          c.tid, c.nt);
+      if constexpr (!TWOSHOT) {
+        for (size_t j = hi_main + c.tid; j < hi; j += c.nt) {
+          Acc<T> acc;
+          acc.init(multimem_ld_reduce_v4<kMm>(c.mc(so) + (j << 4)));
+          if (k.scale != 1.0f) acc.scale(k.scale);
+          const size_t e = j * Tr::K;
+          const int valid = nelem - e < size_t(Tr::K) ? int(nelem - e) : Tr::K;
+          store_unit<T, WIDE>(c.a->out, elem0 + e, acc, valid);
         }
       }
     }
@@ -498,9 +588,9 @@ struct ReducePolicy {
   // slot bytes -> user tensor, widening 16-bit floats to fp32 when WIDE
   __device__ __forceinline__ void copy_out(const char* slot, uint64_t byte_off, uint64_t len) {
     if constexpr (!WIDE) {
-      copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + byte_off, slot, len);
+      copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->out) + byte_off, slot, len);
     } else {
-      const int tid = threadIdx.x, nt = blockDim.x;
+      const int tid = c.tid, nt = c.nt;
       const size_t n16 = (len + 15) >> 4;
       const size_t nelem = len / sizeof(T);
       const size_t elem0 = byte_off / sizeof(T);
@@ -609,6 +699,18 @@ struct MovePolicy {
     else return all;
   }
 
+  // which stages have work on THIS rank (uniform across the CTA)
+  __device__ __forceinline__ bool has_in() const {
+    if constexpr (kTwoPhase || kRootSends) return c.rank == k.root;
+    else return KIND != MV_BARRIER;
+  }
+  __device__ __forceinline__ bool has_mid() const {
+    if constexpr (kTwoPhase || kRootSends) return c.rank != k.root;
+    else if constexpr (KIND == MV_GATHER) return c.rank == k.root;
+    else return KIND != MV_BARRIER;
+  }
+  __device__ __forceinline__ bool has_out() const { return kTwoPhase && c.rank != k.root; }
+
   template <bool MC>
   __device__ __forceinline__ void push(const char* src, uint64_t len, size_t dst_off,
                                        size_t stage_off, uint32_t mask) {
@@ -640,20 +742,20 @@ struct MovePolicy {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j) {
         const char* src = static_cast<const char*>(c.a->list[j]) + off;
-        if (j == c.rank) copy_bytes<LD_USER, 4>(static_cast<char*>(c.a->out) + off, src, len);
+        if (j == c.rank) copy_bytes<LD_USER, 4>(c, static_cast<char*>(c.a->out) + off, src, len);
         else push<false>(src, len, so, so, 1u << j);
       }
     } else if constexpr (KIND == MV_GATHER) {
       const char* src = static_cast<const char*>(c.a->in) + off;
       if (c.rank == k.root) {
-        copy_bytes<LD_USER, 4>(static_cast<char*>(c.a->list[c.rank]) + off, src, len);
+        copy_bytes<LD_USER, 4>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
       } else {
         push<false>(src, len, so + size_t(c.rank) * k.stride, so, 1u << k.root);
       }
     } else if constexpr (KIND == MV_ALLGATHER_PULL) {
       const char* src = static_cast<const char*>(c.a->in) + off;
-      copy_bytes<LD_USER, 4>(c.mine(so), src, len);
-      copy_bytes<LD_USER, 4>(static_cast<char*>(c.a->list[c.rank]) + off, src, len);
+      copy_bytes<LD_USER, 4>(c, c.mine(so), src, len);
+      copy_bytes<LD_USER, 4>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
     } else if constexpr (KIND == MV_ALLGATHER_NVLS) {
       const char* src = static_cast<const char*>(c.a->in) + off;
       const size_t sub = so + size_t(c.rank) * k.stride;
@@ -662,7 +764,7 @@ struct MovePolicy {
       const char* src = static_cast<const char*>(c.a->in) + off;
       const size_t sub = so + size_t(c.rank) * k.stride;
       push<false>(src, len, sub, sub, all & ~(1u << c.rank));
-      copy_bytes<LD_USER, 8>(static_cast<char*>(c.a->list[c.rank]) + off, src, len);
+      copy_bytes<LD_USER, 8>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
     }
   }
 
@@ -673,7 +775,7 @@ struct MovePolicy {
     const size_t so = c.slot_off(c.g0 + t);
     if constexpr (KIND == MV_BROADCAST_P2P || KIND == MV_BROADCAST_NVLS || KIND == MV_SCATTER) {
       if (c.rank == k.root) return;
-      copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + off, c.mine(so), len);
+      copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->out) + off, c.mine(so), len);
     } else if constexpr (kTwoPhase) {
       // phase 2: every non-root rank re-sends its shard to the other non-root ranks, so
       // each of them also receives exactly S bytes and sends at most S.
@@ -690,21 +792,21 @@ struct MovePolicy {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j)
         if (j != c.rank)
-          copy_bytes<LD_SYS, 4>(static_cast<char*>(c.a->list[j]) + off,
+          copy_bytes<LD_SYS, 4>(c, static_cast<char*>(c.a->list[j]) + off,
                                 c.mine(so + size_t(j) * k.stride), len);
     } else if constexpr (KIND == MV_ALLGATHER_PULL) {
       for (int i = 1; i < c.n; ++i) {
         const int p = (c.rank + i) % c.n;  // stagger peers so links load evenly
-        copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->list[p]) + off, c.peer(p, so), len);
+        copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->list[p]) + off, c.peer(p, so), len);
       }
     } else if constexpr (KIND == MV_ALLGATHER_NVLS) {
       for (int j = 0; j < c.n; ++j)
-        copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->list[j]) + off,
+        copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->list[j]) + off,
                               c.mine(so + size_t(j) * k.stride), len);
     } else if constexpr (KIND == MV_ALLGATHER_PUSH) {
       for (int i = 1; i < c.n; ++i) {
         const int j = (c.rank + i) % c.n;
-        copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->list[j]) + off,
+        copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->list[j]) + off,
                               c.mine(so + size_t(j) * k.stride), len);
       }
     }
@@ -715,7 +817,7 @@ struct MovePolicy {
       uint64_t off, len;
       geo.range(t, off, len);
       if (len == 0) return;
-      copy_bytes<LD_SYS, 8>(static_cast<char*>(c.a->out) + off, c.mine(c.slot_off(c.g0 + t)), len);
+      copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->out) + off, c.mine(c.slot_off(c.g0 + t)), len);
     }
   }
 };

@@ -251,7 +251,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   if (max_blocks <= 0) {
     // Bandwidth collectives: enough CTAs to keep ~4 MB in flight per GPU; the rooted
     // movers are limited by one GPU's link so fewer suffice.
-    max_blocks = env_int("PDCC_DEFAULT_CTAS", 256);
+    max_blocks = env_int("PDCC_DEFAULT_CTAS", 128);
   }
   if (max_blocks > ring_limit) max_blocks = ring_limit;
 
@@ -397,7 +397,11 @@ __global__ void __launch_bounds__(kThreads) local_copy_kernel(char* dst, const c
   const uint64_t lo = per * blockIdx.x;
   if (lo >= bytes) return;
   const uint64_t len = bytes - lo < per ? bytes - lo : per;
-  copy_bytes<LD_USER, 8>(dst + lo, src + lo, len);
+  Ctx c{};
+  c.tid = threadIdx.x;
+  c.nt = blockDim.x;
+  c.bar = 0;
+  copy_bytes<LD_USER, 8>(c, dst + lo, src + lo, len);
 }
 
 template <typename T>

@@ -34,6 +34,8 @@
 
 #include "common.h"
 
+#define PDCC_MIN_CTAS_PER_SM_HOST 1  // keep in sync with kMinCtasPerSm (kernels.cuh)
+
 namespace pdcc {
 
 static thread_local char g_err[1024] = "";
@@ -770,9 +772,9 @@ int pdcc_comm_check(pdcc_comm_t* c) {
   return check_block(c->dev.base[c->cfg.rank], c->cfg.rank);
 }
 
-// CTAs of one call must all be resident (they wait on their peers): 2 per SM at most.
+// CTAs of one call must all be resident (they wait on their peers): one per SM.
 static int ring_limit(const pdcc_comm* c) {
-  const int resident = c->sm_count > 0 ? 2 * c->sm_count : c->max_blocks;
+  const int resident = c->sm_count > 0 ? c->sm_count * PDCC_MIN_CTAS_PER_SM_HOST : c->max_blocks;
   return c->max_blocks < resident ? c->max_blocks : resident;
 }
 

@@ -31,7 +31,7 @@ extern "C" {
 #endif
 
 #define PDCC_MAX_RANKS 8      /* one NVSwitch domain of an HGX B200 board      */
-#define PDCC_MAX_BLOCKS 296   /* CTAs (= private tile rings) per collective: 2 per SM */
+#define PDCC_MAX_BLOCKS 148   /* CTAs (= private tile rings) per collective: one per SM */
 #define PDCC_RING_DEPTH 4     /* tile slots per CTA ring                       */
 
 /* error codes */

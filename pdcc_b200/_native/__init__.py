@@ -15,7 +15,7 @@ HERE = Path(__file__).resolve().parent
 LIB_PATH = HERE / "libpdcc.so"
 
 MAX_RANKS = 8
-MAX_BLOCKS = 296
+MAX_BLOCKS = 148
 RING_DEPTH = 4
 
 # enum pdcc_coll
