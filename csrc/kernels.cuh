@@ -228,21 +228,28 @@ __device__ __forceinline__ void store_user_unit(char* base, uint64_t len, size_t
 
 // Push `len` bytes of a user tensor into slot offset `dst_off` of the ranks in `mask` (P2P
 // stores) or of everyone (MC: one multimem.st per 16 bytes). A 16-byte aligned source
-// whose length is a multiple of 16 streams straight from the user tensor; anything else
-// is staged through `stage_off` of this rank's own slot first.
+// whose length is a multiple of 16 streams through the unrolled vector loops; a ragged
+// tail or an odd view is assembled byte-exactly, one unit per thread, and stored as whole
+// 16-byte units all the same (slots have room). No staging and no barrier either way, so
+// the two warp teams of run_pipeline() never have to synchronise inside a stage.
 template <bool MC>
 __device__ __forceinline__ void push_user(const Ctx& c, const char* src, uint64_t len,
-                                          size_t dst_off, size_t stage_off, uint32_t mask) {
+                                          size_t dst_off, size_t /*stage_off*/, uint32_t mask) {
   if (len == 0 || (!MC && mask == 0)) return;
   if (aligned16(src) && (len & 15u) == 0) {
     if constexpr (MC) push_mc<LD_USER, 8>(c, dst_off, src, len);
     else push_p2p<LD_USER, 8>(c, dst_off, src, len, mask);
-  } else {
-    copy_bytes<LD_USER, 4>(c, c.mine(stage_off), src, len);
-    team_sync(c);
-    if constexpr (MC) push_mc<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len);
-    else push_p2p<LD_SYS, 8>(c, dst_off, c.mine(stage_off), len, mask);
-    team_sync(c);
+    return;
+  }
+  const size_t n16 = size_t((len + 15) >> 4);
+  for (size_t j = c.tid; j < n16; j += c.nt) {
+    const uint4 v = load_user_unit(src, len, j);
+    if constexpr (MC) {
+      multimem_st_v4(c.mc(dst_off) + (j << 4), v);
+    } else {
+      for (int p = 0; p < c.n; ++p)
+        if ((mask >> p) & 1u) st_v4(c.peer(p, dst_off) + (j << 4), v);
+    }
   }
 }
 
