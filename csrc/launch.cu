@@ -191,6 +191,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
         // themselves (two-phase, unicast stores, S bytes per GPU and direction).
         const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
         if (n <= 2) algo = PDCC_ALGO_P2P;
+        else if (mc_ok && n <= 4) algo = PDCC_ALGO_NVLS;  // measured: replication to <= 3 peers keeps up
         else if (bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
         else algo = mc_ok ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       } else {
@@ -259,6 +260,8 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   if (nb <= 0) {
     const uint64_t per_cta = 32 << 10;  // below this a CTA is latency- not bandwidth-bound
     nb = int(ceil_div(bytes ? bytes : 1, per_cta));
+    // big messages: every SM pushes (NVLink stores are limited per SM, profiles/)
+    if (bytes >= (uint64_t(8) << 20) && env_int("PDCC_DEFAULT_CTAS", 0) <= 0) max_blocks = ring_limit;
     if (nb > max_blocks) nb = max_blocks;
     if (nb < 1) nb = 1;
   }
@@ -268,8 +271,15 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   }
 
   uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
-  // aim for >= 4 tiles per CTA on big messages so staging overlaps the NVLink phase
-  uint64_t tile = per_cta / 4;
+  // Every tile costs one flag round (a system fence that drains the CTA's outstanding
+  // NVLink stores plus the flag's flight, ~5 us). Symmetric collectives load all links
+  // evenly in every stage, so they take the largest tile that fits the slot. The
+  // two-phase rooted collectives load different links in different stages and only reach
+  // link rate when the stages of neighbouring tiles overlap, so they are cut finer.
+  const bool rooted_two_phase = (twoshot_push && op.coll == PDCC_REDUCE) || bcast_2p;
+  uint64_t split = uint64_t(env_int("PDCC_TILE_SPLIT", 0));
+  if (split == 0) split = rooted_two_phase ? 8 : 1;
+  uint64_t tile = per_cta / split;
   const uint64_t min_tile = 64 << 10;
   if (tile < min_tile) tile = per_cta < min_tile ? per_cta : min_tile;
   tile = round_up(tile, align);

@@ -403,7 +403,7 @@ static int fill_dev(pdcc_comm* c) {
 }
 
 static void sizes_from_cfg(pdcc_comm* c) {
-  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(1) << 20);
+  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(2) << 20);
   c->max_blocks = c->cfg.max_blocks > 0 ? c->cfg.max_blocks : PDCC_MAX_BLOCKS;
   if (c->max_blocks > PDCC_MAX_BLOCKS) c->max_blocks = PDCC_MAX_BLOCKS;
   c->heap_off = kDataOffset + size_t(c->max_blocks) * PDCC_RING_DEPTH * c->slot_bytes;

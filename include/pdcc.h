@@ -113,7 +113,7 @@ typedef struct {
   int multicast;          /* -1 auto, 0 never, 1 require                      */
   int timeout_ms;         /* host-side rendezvous timeout                     */
   int device_timeout_ms;  /* device-side flag wait timeout (0 = default 10 s) */
-  size_t slot_bytes;      /* per-CTA tile slot capacity (0 = default 1 MiB)   */
+  size_t slot_bytes;      /* per-CTA tile slot capacity (0 = default 2 MiB)   */
   int max_blocks;         /* rings to provision (0 = PDCC_MAX_BLOCKS)         */
   size_t heap_bytes;      /* symmetric heap for zero-copy tensors (0 = none)  */
   char key[64];           /* unique per group: namespaces the store keys      */
