@@ -272,13 +272,14 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
 
   uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
   // Every tile costs one flag round (a system fence that drains the CTA's outstanding
-  // NVLink stores plus the flag's flight, ~5 us). Symmetric collectives load all links
-  // evenly in every stage, so they take the largest tile that fits the slot. The
-  // two-phase rooted collectives load different links in different stages and only reach
-  // link rate when the stages of neighbouring tiles overlap, so they are cut finer.
+  // NVLink stores plus the flag's flight, ~5 us), but only neighbouring tiles overlap
+  // their stages (staging copies under the NVLink phase; the two link directions of the
+  // rooted two-phase collectives). Measured on 8xB200 at 256 MiB (profiles/final_n8.md):
+  // all_reduce 972 / 786 us with 1 / 4 tiles per CTA, reduce 745 / 662 / 627 us and
+  // broadcast 775 / 589 / 585 us with 1 / 4 / 8.
   const bool rooted_two_phase = (twoshot_push && op.coll == PDCC_REDUCE) || bcast_2p;
   uint64_t split = uint64_t(env_int("PDCC_TILE_SPLIT", 0));
-  if (split == 0) split = rooted_two_phase ? 8 : 1;
+  if (split == 0) split = rooted_two_phase ? 8 : 4;
   uint64_t tile = per_cta / split;
   const uint64_t min_tile = 64 << 10;
   if (tile < min_tile) tile = per_cta < min_tile ? per_cta : min_tile;

@@ -17,7 +17,7 @@ _REASONS = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_pow
 class ClockSampler:
     """with ClockSampler(gpu_index) as cs: <timed region>; cs.summary() -> dict"""
 
-    def __init__(self, gpu_index: int = 0, period_ms: int = 100):
+    def __init__(self, gpu_index: int = 0, period_ms: int = 50):
         self.gpu_index, self.period_ms = gpu_index, period_ms
         self.samples: List[dict] = []
         self._proc: Optional[subprocess.Popen] = None
@@ -47,9 +47,14 @@ class ClockSampler:
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self._thread = threading.Thread(target=self._reader, daemon=True)
             self._thread.start()
-            self.t0 = time.monotonic()
+            # nvidia-smi needs a moment to come up; wait for its first line so that even a
+            # timed region of a few tens of ms is bracketed by samples
+            deadline = time.monotonic() + 3.0
+            while not self.samples and time.monotonic() < deadline:
+                time.sleep(0.01)
         except OSError:
             self._proc = None
+        self.t0 = time.monotonic()
         return self
 
     def __exit__(self, *exc) -> None:
@@ -67,7 +72,7 @@ class ClockSampler:
     def summary(self) -> dict:
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        inside = [s for s in self.samples if self.t0 <= s["t"] <= self.t1 + 0.3] or self.samples
+        inside = [s for s in self.samples if self.t0 - 0.06 <= s["t"] <= self.t1 + 0.3] or self.samples
         reasons = sorted({r for s in inside for r in s["reasons"]})
         return {"sm_mhz": statistics.median(s["sm"] for s in inside),
                 "sm_max_mhz": max(s["max"] for s in inside),
