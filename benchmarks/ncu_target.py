@@ -2,6 +2,10 @@
 world-size-1 all_reduce (tile pipeline with self-signalled flags) and one 4-rank emulated
 two-shot all_reduce (one cooperative kernel over all ranks' data, as B200_PROFILING.md asks
 for when there are fewer GPUs than ranks)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from pdcc_b200.ops import collectives as K
 
