@@ -401,7 +401,7 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
 // K9 local helpers: the world-size-1 degenerate collectives (a list op over one rank is a
 // copy) and the DP demo's scale+cast when there is nobody to reduce with.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) local_copy_kernel(char* dst, const char* src,
+__global__ void __launch_bounds__(kThreads, 2) local_copy_kernel(char* dst, const char* src,
                                                               uint64_t bytes) {
   // each CTA takes a contiguous span so its loads stream
   const uint64_t per = round_up_dev(ceil_div_dev(bytes, gridDim.x), 16);
