@@ -235,6 +235,26 @@ int pdcc_emu_collective(pdcc_emu_t* emu, const pdcc_op_t* ops, void* stream);
 int pdcc_emu_check(pdcc_emu_t* emu);
 
 /* ------------------------------------------------------------------------ *
+ * Allocation-free variant of the two-rank emulated all_reduce. It has no
+ * counterpart in the reference. For callers that cannot allocate device memory
+ * when they need the collective (a plugin running after its host application
+ * took all device memory into its own pool; a loop that cannot afford
+ * cudaMalloc's device-wide synchronisation): the two symmetric blocks live in a
+ * static __device__ array of about 44 MiB that every GPU loading the library
+ * holds until exit. In-place SUM/PRODUCT/MIN/MAX over buf0 and buf1 (count
+ * elements each, both on `device`); afterwards both hold the result.
+ *   - count * sizeof(dtype) must not exceed PDCC_NOALLOC_MAX_BYTES.
+ *   - The first call on a device resolves the array's device address and zeroes
+ *     its flags; it synchronises, so make it before any stream capture.
+ *   - All calls on a device share the array: run them on one stream; calls
+ *     that overlap on the GPU race.
+ *   - Calls no cudaMalloc / cudaFree / allocating routine.
+ * ------------------------------------------------------------------------ */
+#define PDCC_NOALLOC_MAX_BYTES (64ull << 20)
+int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, uint64_t count, int dtype,
+                                 int redop, void* stream);
+
+/* ------------------------------------------------------------------------ *
  * K9  Local helpers used by the world-size-1 degenerate paths and by the
  * DP demo: strided-free vector copy and fused scale+cast.
  * ------------------------------------------------------------------------ */

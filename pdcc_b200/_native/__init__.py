@@ -142,6 +142,7 @@ def lib() -> C.CDLL:
         "pdcc_gather": [vp, vp, C.POINTER(vp), C.c_uint64, ci, ci, vp],
         "pdcc_all_gather": [vp, C.POINTER(vp), vp, C.c_uint64, ci, vp],
         "pdcc_barrier": [vp, vp],
+        "pdcc_emu2_all_reduce_noalloc": [ci, vp, vp, C.c_uint64, ci, ci, vp],
     }
     for name, argtypes in sigs.items():
         fn = getattr(L, name)
