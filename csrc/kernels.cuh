@@ -314,7 +314,7 @@ __device__ __noinline__ void combine_main(const char* __restrict__ user,
   }
 }
 
-// Hot loop of the NVLS reductions over units [lo, hi) of a slot: 8 multimem.ld_reduce in
+// Hot loop of the NVLS reductions over units [lo, hi) of a slot: 16 multimem.ld_reduce in
 // flight per thread, then either the replicated store (all_reduce two-shot), a plain store
 // into the root's slot (rooted two-shot) or the vector store to the user tensor (one-shot).
 template <typename T, int KMM, bool TWOSHOT, bool ROOTED, bool WIDE>
@@ -322,7 +322,10 @@ __device__ __noinline__ void nvls_units(char* __restrict__ mc, char* __restrict_
                                         void* __restrict__ out, size_t lo, size_t hi, float scale,
                                         int tid, int nt) {
   using Tr = Traits<T>;
-  constexpr int U = 8;
+  // 16 reductions in flight per thread: this loop usually runs on one half of the CTA
+  // (the other half stages the next tile), and a multimem.ld_reduce is a full round trip
+  // through the switch, so the in-flight bytes per SM have to come from the unroll.
+  constexpr int U = 16;
   const bool scaled = scale != 1.0f;
   for (size_t j0 = lo + tid; j0 < hi; j0 += size_t(nt) * U) {
     uint4 v[U];

@@ -294,3 +294,35 @@ def native_sweep(rank, size):
         failures.append(("device", str(e)))
     _save(rank, "sweep", {"failures": failures, "checked": checked,
                           "multicast": comm.has_multicast, "handle": comm.handle_kind})
+
+
+def dp_mlp_check(rank, size):
+    """D1: bucketed gradient averaging == one big-batch step (README.md:5), any backend."""
+    from pdcc_b200.models.mlp import MLP, DataParallelTrainer
+
+    dev = demos.device()
+    dtype = torch.float32
+    torch.manual_seed(1234 + rank)  # ranks start with DIFFERENT params: broadcast must fix it
+    model = MLP(hidden=32, layers=3, dtype=dtype, device=dev)
+    tr = DataParallelTrainer(model, lr=0.1, bucket_bytes=3000)  # several buckets
+    g = torch.Generator(device="cpu").manual_seed(7)
+    xs = torch.randn(size, 8, 32, generator=g)
+    ys = torch.randn(size, 8, 32, generator=g)
+    losses = []
+    for _ in range(3):
+        losses.append(float(tr.step(xs[rank].to(dev), ys[rank].to(dev))))
+    if dev.type == "cuda":
+        torch.cuda.synchronize()
+
+    # single-process oracle: rank 0's initial parameters, the concatenated batch
+    torch.manual_seed(1234)
+    ref = MLP(hidden=32, layers=3, dtype=dtype)
+    opt = torch.optim.SGD(ref.parameters(), lr=0.1)
+    for _ in range(3):
+        opt.zero_grad()
+        loss = torch.nn.functional.mse_loss(ref(xs.reshape(-1, 32)), ys.reshape(-1, 32))
+        loss.backward()
+        opt.step()
+    err = max(float((p.detach().cpu() - q.detach()).abs().max())
+              for p, q in zip(model.parameters(), ref.parameters()))
+    _save(rank, "dp", {"err": err, "losses": losses, "buckets": len(tr.avg.buckets)})

@@ -64,3 +64,13 @@ def test_sweep_correctness_native(tmp_path):
         res = torch.load(os.path.join(tmp_path, f"sweep_{r}.pt"))
         assert res["failures"] == [], res["failures"][:5]
         assert res["checked"] > 50
+
+
+def test_data_parallel_native(tmp_path):
+    """D1 on real GPUs: broadcast + bucketed fused all_reduce_avg overlapped with backward."""
+    n = min(_world(), 4)
+    dist.launch(_workers.dp_mlp_check, size=n, backend="b200", timeout=300,
+                env={"PDCC_TEST_OUT": str(tmp_path)})
+    for r in range(n):
+        res = torch.load(os.path.join(tmp_path, f"dp_{r}.pt"))
+        assert res["err"] < 1e-4, res
