@@ -96,10 +96,10 @@ __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
 // One flag round per tile. Iteration t
 //   (1) waits for everything it is about to consume: the slot of tile t+1 being free
 //       (DONE of tile t+1-DEPTH), READY(t), and MID(t-1) when there is an OUT stage;
-//   (2) runs IN(t+1), MID(t) and OUT(t-1) AT THE SAME TIME on two teams of warps — the push
-//       of the next tile (NVLink egress, or a local copy-in) overlaps the combine / re-send
-//       / copy-out of the current one, so the stages that load different links (or HBM)
-//       never idle each other, even when all CTAs of all ranks run in lockstep;
+//   (2) runs IN(t+1) + OUT(t-1) and MID(t) AT THE SAME TIME on two teams of warps — the
+//       push (or copy-in) of the next tile and the copy-out of the previous one overlap the
+//       combine / re-send of the current one, so the stages that load different links (or
+//       HBM) never idle each other, even when all CTAs of all ranks run in lockstep;
 //   (3) publishes READY(t+1), MID(t) and DONE with ONE system fence.
 // A rank that has only one kind of work in a collective (the root of a scatter only pushes,
 // the others only copy out) keeps all its threads on it.
@@ -148,13 +148,18 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
     const int jobs = int(do_in) + int(has_mid) + int(do_out);
     if (jobs >= 2) {
       split();
-      if (do_in) {  // team A pushes the next tile, team B finishes the current ones
+      if (do_in && has_mid) {
+        // team A: the local / egress side (push or copy-in of the next tile, then the
+        // copy-out of the previous one); team B: the combine / re-send of the current tile
         if (team_a) {
           p.in(t + 1);
-        } else {
-          if (has_mid) p.mid(t);
           if (do_out) p.out(t - 1);
+        } else {
+          p.mid(t);
         }
+      } else if (do_in) {  // no MID on this rank (root of a rooted reduce): push vs copy-out
+        if (team_a) p.in(t + 1);
+        else p.out(t - 1);
       } else {  // no IN on this rank: re-send and copy-out side by side
         if (team_a) p.out(t - 1);
         else p.mid(t);
