@@ -9,6 +9,7 @@
 #include <atomic>
 
 #include "ll.cuh"
+#include "tma_copy.cuh"
 
 namespace pdcc {
 
@@ -461,11 +462,35 @@ int pdcc_local_copy(void* dst, const void* src, uint64_t bytes, int device, void
   if (!dst || !src) return PDCC_EINVAL;
   int rc = set_device_checked(device);
   if (rc) return rc;
-  uint64_t blocks = (bytes + (64 << 10) - 1) / (64 << 10);
-  if (blocks > 4 * 148) blocks = 4 * 148;
-  local_copy_kernel<<<dim3(unsigned(blocks)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<char*>(dst), static_cast<const char*>(src), bytes);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e;
+  const bool tma_ok = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src) | bytes) & 15u) == 0 &&
+                      bytes >= (uint64_t(1) << 20) && env_int("PDCC_COPY_TMA", 1) != 0;
+  if (tma_ok) {
+    // big aligned copies go through the TMA engine (tma_copy.cuh), two CTAs per SM
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+      e = cudaFuncSetAttribute(tma_copy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               int(kTmaSmemBytes));
+      if (e != cudaSuccess) {
+        set_error("tma_copy attribute: %s", cudaGetErrorString(e));
+        return PDCC_ECUDA;
+      }
+      attr_set[dev] = true;
+    }
+    uint64_t chunks = (bytes + kTmaChunk - 1) / kTmaChunk;
+    uint64_t blocks = chunks < 2 * 148 ? chunks : 2 * 148;
+    tma_copy_kernel<<<dim3(unsigned(blocks)), dim3(32), kTmaSmemBytes,
+                      static_cast<cudaStream_t>(stream)>>>(static_cast<char*>(dst),
+                                                           static_cast<const char*>(src), bytes);
+  } else {
+    uint64_t blocks = (bytes + (64 << 10) - 1) / (64 << 10);
+    if (blocks > 4 * 148) blocks = 4 * 148;
+    local_copy_kernel<<<dim3(unsigned(blocks)), dim3(kThreads), 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<char*>(dst), static_cast<const char*>(src), bytes);
+  }
+  e = cudaGetLastError();
   if (e != cudaSuccess) {
     set_error("local_copy launch: %s", cudaGetErrorString(e));
     return PDCC_ECUDA;

@@ -20,7 +20,8 @@ def test_probe_reports_b200_capabilities():
 
 
 def test_local_copy_and_scale_cast():
-    for nbytes in (1, 15, 16, 4097, 1 << 20, (1 << 24) + 3):
+    # >= 1 MiB, 16-byte aligned sizes take the TMA bulk-copy kernel (multi-chunk, ring wrap)
+    for nbytes in (1, 15, 16, 4097, 1 << 20, (1 << 20) + 16, (1 << 24) + 3, 48 << 20, 256 << 20):
         src = torch.randint(0, 255, (nbytes,), dtype=torch.uint8, device="cuda")
         dst = torch.zeros_like(src)
         K.local_copy(dst, src)
