@@ -792,6 +792,26 @@ int pdcc_plan(pdcc_comm_t* c, const pdcc_op_t* op, int* algo, int* nblocks, int*
   return PDCC_OK;
 }
 
+int pdcc_plan_dry(int nranks, int has_multicast, size_t slot_bytes, int rings, const pdcc_op_t* op,
+                  int* algo, int* nblocks, int* threads, uint64_t* tile_bytes, int* ntiles) {
+  if (!op || nranks < 1 || nranks > PDCC_MAX_RANKS) return PDCC_EINVAL;
+  DevComm dev;
+  memset(&dev, 0, sizeof(dev));
+  dev.rank = 0;
+  dev.nranks = nranks;
+  dev.slot_bytes = uint32_t(slot_bytes ? slot_bytes : (size_t(2) << 20));
+  dev.mc = has_multicast ? reinterpret_cast<char*>(uintptr_t(16)) : nullptr;  // never dereferenced
+  Plan p;
+  int rc = plan_collective(dev, rings > 0 ? rings : PDCC_MAX_BLOCKS, has_multicast != 0, *op, &p);
+  if (rc) return rc;
+  if (algo) *algo = p.algo;
+  if (nblocks) *nblocks = p.nblocks;
+  if (threads) *threads = p.threads;
+  if (tile_bytes) *tile_bytes = p.tile_bytes;
+  if (ntiles) *ntiles = p.ntiles;
+  return PDCC_OK;
+}
+
 static int validate_ptrs(const pdcc_op_t& op, int rank, int n) {
   if (op.count == 0 || op.coll == PDCC_BARRIER) return PDCC_OK;
   auto need = [&](const void* p, const char* what) {

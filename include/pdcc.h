@@ -216,6 +216,12 @@ int pdcc_barrier(pdcc_comm_t* comm, void* stream);
 int pdcc_plan(pdcc_comm_t* comm, const pdcc_op_t* op, int* algo, int* nblocks, int* threads,
               uint64_t* tile_bytes, int* ntiles);
 
+/* The same planner without a communicator (and without a GPU): what AUTO would resolve to
+ * for `op` on a group of `nranks` with `slot_bytes` slots and `rings` usable CTAs, with or
+ * without a multicast mapping. Used by the CPU tests of the size -> variant table. */
+int pdcc_plan_dry(int nranks, int has_multicast, size_t slot_bytes, int rings, const pdcc_op_t* op,
+                  int* algo, int* nblocks, int* threads, uint64_t* tile_bytes, int* ntiles);
+
 /* Number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim is read from here, not estimated). */
 uint64_t pdcc_launch_count(void);

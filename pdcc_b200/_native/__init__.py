@@ -128,6 +128,8 @@ def lib() -> C.CDLL:
         "pdcc_collective": [vp, C.POINTER(Op), vp],
         "pdcc_plan": [vp, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci),
                       C.POINTER(C.c_uint64), C.POINTER(ci)],
+        "pdcc_plan_dry": [ci, ci, C.c_size_t, ci, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci),
+                          C.POINTER(ci), C.POINTER(C.c_uint64), C.POINTER(ci)],
         "pdcc_emu_create": [ci, ci, C.c_size_t, ci, ci, C.POINTER(vp)],
         "pdcc_emu_destroy": [vp],
         "pdcc_emu_collective": [vp, C.POINTER(Op), vp],
@@ -155,6 +157,22 @@ def lib() -> C.CDLL:
 def check(rc: int) -> None:
     if rc != 0:
         raise PdccError(rc, lib().pdcc_last_error().decode(errors="replace"))
+
+
+def plan_dry(nranks: int, coll: int, count: int, dtype: int, *, has_multicast: bool = True,
+             slot_bytes: int = 0, rings: int = 0, redop: int = 0, algo: int = 0,
+             nblocks: int = 0) -> dict:
+    """AUTO planning without a communicator or a GPU (see pdcc_plan_dry)."""
+    op = Op()
+    op.coll, op.dtype, op.out_dtype, op.redop = coll, dtype, dtype, redop
+    op.algo, op.nblocks, op.scale, op.count = algo, nblocks, 1.0, count
+    a, b, t, n = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    tb = C.c_uint64()
+    check(lib().pdcc_plan_dry(nranks, int(has_multicast), slot_bytes, rings, C.byref(op),
+                              C.byref(a), C.byref(b), C.byref(t), C.byref(tb), C.byref(n)))
+    names = {v: k for k, v in ALGO_NAMES.items()}
+    return {"algo": names.get(a.value, a.value), "nblocks": b.value, "threads": t.value,
+            "tile_bytes": tb.value, "ntiles": n.value}
 
 
 def launch_count() -> int:
