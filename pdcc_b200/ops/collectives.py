@@ -12,6 +12,7 @@ global->group rank translation live one layer up in pdcc_b200/distributed.py.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional, Sequence
 
 import torch
@@ -27,6 +28,8 @@ _REDUCIBLE = {torch.float32, torch.bfloat16, torch.float16, torch.float64, torch
               torch.int64, torch.uint8}
 
 SUM, AVG, PRODUCT, MIN, MAX = 0, 1, 2, 3, 4
+_NVTX = os.environ.get("PDCC_NVTX", "0") == "1"
+_COLL_NAMES = ("all_reduce", "reduce", "broadcast", "scatter", "gather", "all_gather", "barrier")
 
 
 def dtype_code(dtype: torch.dtype, reduce: bool = False) -> int:
@@ -114,8 +117,12 @@ class NativeComm:
 
     # -- plumbing ---------------------------------------------------------------------
     def _run(self, op: N.Op, stream: Optional[torch.cuda.Stream]) -> None:
+        if _NVTX:  # one NVTX range per collective, off unless PDCC_NVTX=1
+            torch.cuda.nvtx.range_push(f"pdcc.{_COLL_NAMES[op.coll]}[{op.count}]")
         rc = self._collective(self._h, self._op_ref if op is self._op else C.byref(op),
                               _stream_ptr(stream, self.device))
+        if _NVTX:
+            torch.cuda.nvtx.range_pop()
         if rc != 0:
             N.check(rc)
 
