@@ -67,11 +67,11 @@ struct Plan {
   int algo;
   int nblocks;
   int threads;
-  uint64_t tile_bytes;  // payload bytes per CTA per tile (see kernels.cu)
+  uint64_t tile_bytes;  // payload bytes per CTA per tile (see kernels.cuh)
   int ntiles;
 };
 
-// kernels.cu
+// launch.cu
 // ring_limit: how many CTAs (= provisioned rings, capped by the SM count) a call may use.
 int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc_op_t& op,
                     Plan* plan);

@@ -172,6 +172,8 @@ struct Ctx {
   __device__ __forceinline__ char* mc(size_t off) const { return a->comm.mc + off; }
 };
 
+// Named-barrier sync of the current team. Not used by the shipped stages (they are
+// barrier-free by construction); kept for stages that may need an intra-team hand-off.
 __device__ __forceinline__ void team_sync(const Ctx& c) {
   asm volatile("bar.sync %0, %1;" ::"r"(c.bar), "r"(c.nt) : "memory");
 }

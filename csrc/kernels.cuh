@@ -6,16 +6,16 @@
 // ring's lifetime tile count. Per tile a rank runs up to three stages and raises one
 // monotonic flag per stage on its peers:
 //
-//   IN   user tensor -> slot(s), local or pushed to peers      -> READY(g)
-//   MID  wait READY; cross-GPU read/reduce/(push)              -> MID(g)   [two-shot only]
-//   OUT  wait MID;   slot -> user tensor                        -> DONE(g)
+//   IN   user tensor -> slot(s): pushed to peers, or copied locally   -> READY(g)
+//   MID  wait READY; combine / re-send / copy-out                     -> MID(g)  [two-shot]
+//   OUT  wait MID;   slot -> user tensor                              -> DONE(g)
 //
 // and before touching ring position g % DEPTH again every rank waits for DONE(g-DEPTH)
 // from all ranks. Because the counters never reset and every collective obeys the same
 // slot discipline, consecutive calls of *different* collectives pipeline into each other
 // with no end-of-kernel barrier and no host-side epoch (so launches are graph-capturable).
-// IN(t+1) is issued before MID(t) and OUT(t-1) after it, so the NVLink phase of one tile
-// overlaps the HBM staging of its neighbours across the CTAs of a GPU.
+// run_pipeline() runs IN(t+1)/OUT(t-1) and MID(t) side by side on two warp teams with one
+// flag round per tile.
 //
 // Reference parity: one kernel per torch.distributed call site of main.py (lines cited
 // at each policy). The reference itself has no kernels.
@@ -41,7 +41,7 @@ struct KArgs {
   int root;
   int redop;
   float scale;
-  int stagger;  // odd CTAs run their IN stage one tile further ahead (see run_pipeline)
+  int stagger;  // reserved (the staggered-lookahead experiment of round 1; unused by v2)
 };
 
 struct Geo {
