@@ -326,3 +326,54 @@ def dp_mlp_check(rank, size):
     err = max(float((p.detach().cpu() - q.detach()).abs().max())
               for p, q in zip(model.parameters(), ref.parameters()))
     _save(rank, "dp", {"err": err, "losses": losses, "buckets": len(tr.avg.buckets)})
+
+
+def api_misc(rank, size):
+    """Lifecycle and bookkeeping of the API layer on the gloo path."""
+    res = {}
+    res["rank"], res["world"], res["backend"] = dist.get_rank(), dist.get_world_size(), dist.get_backend()
+    res["initialized"] = dist.is_initialized()
+    try:
+        dist.init_process_group("gloo", rank=rank, world_size=size)
+    except ValueError as e:
+        res["double_init"] = str(e)
+    g = dist.new_group([0, size - 1])
+    if g != dist.GroupMember.NON_GROUP_MEMBER:
+        res["group_size"] = dist.get_world_size(g)
+        res["group_rank"] = dist.get_rank(g)
+        res["global_of_1"] = dist.get_global_rank(g, 1)
+        res["group_of_last"] = dist.get_group_rank(g, size - 1)
+        try:
+            dist.broadcast(torch.zeros(1), src=1 if size > 2 else 5, group=g)
+        except ValueError as e:
+            res["bad_src"] = str(e)
+        # group_src / group_dst spellings
+        t = torch.tensor([float(rank)])
+        dist.broadcast(t, group=g, group_src=1)
+        res["bcast_group_src"] = t.item()
+        t = torch.tensor([1.0])
+        dist.reduce(t, group=g, group_dst=0)
+        res["reduce_group_dst"] = t.item()
+        w = dist.barrier(group=g, async_op=True)
+        w.wait()
+        res["barrier_done"] = w.is_completed()
+        dist.destroy_process_group(g)
+    else:
+        res["sentinel_rank"] = dist.get_rank(g)
+        res["sentinel_size"] = dist.get_world_size(g)
+    try:
+        dist.all_reduce(torch.zeros(1), op=17)
+    except ValueError as e:
+        res["bad_op"] = str(e)
+    try:
+        dist.all_reduce(torch.zeros(1), group="nope")
+    except TypeError as e:
+        res["bad_group"] = str(e)
+    if torch.cuda.is_available() is False:
+        try:
+            # CPU-only box: a "CUDA" request cannot be served by the gloo backend
+            dist.native_comm()
+        except RuntimeError as e:
+            res["native_on_gloo"] = str(e)
+    dist.barrier()
+    _save(rank, "api", res)
