@@ -140,7 +140,10 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       if (n <= 2) {
         algo = PDCC_ALGO_ONESHOT_P2P;
       } else if (bytes <= uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 1 << 20))) {
-        algo = PDCC_ALGO_ONESHOT_P2P;
+        // one multimem.ld_reduce per unit instead of n-1 pushed copies: measured at
+        // 8 GPUs, 256 KiB: 17.4 us vs 20.7 us (profiles/sweep_n8_v1.jsonl, graph-timed)
+        algo = (nvls && n > env_int("PDCC_NVLS_MIN_RANKS", 4)) ? PDCC_ALGO_ONESHOT_NVLS
+                                                               : PDCC_ALGO_ONESHOT_P2P;
       } else {
         algo = (nvls && n > env_int("PDCC_NVLS_MIN_RANKS", 4)) ? PDCC_ALGO_TWOSHOT_NVLS
                                                                : PDCC_ALGO_TWOSHOT_P2P;

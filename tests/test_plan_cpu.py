@@ -54,7 +54,9 @@ def test_every_auto_plan_fits_the_slot_layout(n, mc):
 def test_selection_follows_the_measured_crossovers():
     ar = lambda n, b, **kw: _plan(n, N.ALL_REDUCE, b, **kw)[0]["algo"]  # noqa: E731
     assert ar(8, 4096) == "ll" and ar(2, 200 << 10) == "ll"
-    assert ar(8, 128 << 10) == "oneshot_p2p"            # above 512 KiB / n, below 1 MiB
+    assert ar(8, 128 << 10) == "oneshot_nvls"           # above 512 KiB / n, below 1 MiB
+    assert ar(8, 128 << 10, has_multicast=False) == "oneshot_p2p"
+    assert ar(4, 512 << 10) == "oneshot_p2p"            # NVLS only beyond 4 ranks (measured)
     assert ar(2, 1 << 30) == "oneshot_p2p"              # n = 2: one-shot moves no more bytes
     assert ar(4, 256 << 20) == "twoshot_p2p"            # measured: push beats NVLS up to 4 ranks
     assert ar(8, 256 << 20) == "twoshot_nvls"
