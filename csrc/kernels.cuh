@@ -371,16 +371,17 @@ __device__ __noinline__ void nvls_units(char* __restrict__ mc, char* __restrict_
   }
 }
 
-// Slot layouts (offsets from the tile's slot, `tile` = KArgs::tile_bytes, `sub` = tile/n):
+// Slot layouts (offsets from the tile's slot, `tile` = KArgs::tile_bytes, `sub` = tile/owners):
 //   one-shot P2P  A[q] at q*stride            rank q's whole tile        (tile <= slot/n)
 //   two-shot P2P  A[q] at q*sub               rank q's partial of MY chunk
-//                 B[j] at tile + j*sub        reduced chunk j from its owner  (tile <= slot/2)
+//                 B[o] at (n + o)*sub         reduced chunk o from its owner
+//                 (owners: all n ranks, or the n-1 non-root ranks of a rooted reduce)
 //   NVLS          the tile itself at 0        (multicast-addressable copy-in)
 //
 // The P2P variants are write-based: every byte that crosses NVLink is a posted store issued
 // straight from the user tensor (IN) or from registers (MID); all loads are local. Remote
 // loads cost a round trip per 16 bytes and measured 2-3x slower than stores on B200
-// (profiles/sweep_n2_pull_vs_push.md), so nothing here pulls.
+// (profiles/sweep_n2_pull_baseline.jsonl vs sweep_n2_push.jsonl), so nothing here pulls.
 template <typename T, bool WIDE, int OP, int ALGO, bool ROOTED>
 struct ReducePolicy {
   using Tr = Traits<T>;
