@@ -56,6 +56,10 @@ def main() -> None:
     ap.add_argument("--nblocks", default="0", help="comma list of CTA counts (0 = auto)")
     ap.add_argument("--out", default="gpurun_out/sweep.jsonl")
     ap.add_argument("--subgroup", default="", help="comma list of global ranks, e.g. 1,3")
+    ap.add_argument("--sizes", default="", help="explicit comma list of sizes (overrides min/max/factor)")
+    ap.add_argument("--env-sweep", default="",
+                    help="A/B a planner knob inside ONE job, e.g. PDCC_TILE_SPLIT=0,1,4,8 "
+                         "(the native planner reads its knobs from the environment per call)")
     ap.add_argument("--graph", action="store_true",
                     help="also time small messages captured in a CUDA graph (device-only latency)")
     ap.add_argument("--graph-max", type=parse_size, default=1 << 20)
@@ -97,10 +101,17 @@ def main() -> None:
     kop = int(op_p)
 
     sizes = []
-    s = parse_size(args.min)
-    while s <= parse_size(args.max):
-        sizes.append(s)
-        s *= args.factor
+    if args.sizes:
+        sizes = [parse_size(x) for x in args.sizes.split(",")]
+    else:
+        s = parse_size(args.min)
+        while s <= parse_size(args.max):
+            sizes.append(s)
+            s *= args.factor
+    env_name, env_values = None, [None]
+    if args.env_sweep:
+        env_name, vals = args.env_sweep.split("=", 1)
+        env_values = vals.split(",")
 
     def timed(fn, nbytes: int) -> float:
         iters = 200 if nbytes <= (1 << 16) else 50 if nbytes <= (1 << 22) else 10 if nbytes <= (1 << 28) else 5
@@ -199,7 +210,11 @@ def main() -> None:
             for impl in impls:
                 variants = [("nccl", 0)] if impl == "nccl" else \
                     [(a, int(nb)) for a in algos for nb in args.nblocks.split(",")]
-                for algo, nb in variants:
+                variants = [(a, nb, ev) for (a, nb) in variants
+                            for ev in (env_values if impl == "pdcc" else [None])]
+                for algo, nb, ev in variants:
+                    if env_name is not None and ev is not None:
+                        os.environ[env_name] = ev  # same value on every rank: same plan
                     if algo == "ll" and real > (1 << 20):
                         continue  # LL doubles the wire bytes: a small-message variant only
                     if not member or (impl == "pdcc" and comm is None):
@@ -220,6 +235,8 @@ def main() -> None:
                            "busbw_GBps": round(algbw * BUS[coll](n), 2),
                            "roofline_frac": round(roof_us / us, 3) if us > 0 else None, "n": n,
                            "graph_us": graph_us}
+                    if env_name is not None and impl == "pdcc":
+                        row["env"] = {env_name: ev}
                     if impl == "pdcc":
                         row["plan"] = comm.plan({"all_reduce": 0, "reduce": 1, "broadcast": 2,
                                                  "scatter": 3, "gather": 4, "all_gather": 5}[coll],
@@ -231,7 +248,8 @@ def main() -> None:
                     if rank == 0:
                         out.write(json.dumps(row) + "\n")
                         out.flush()
-                        print(f"{coll:11s} {impl:5s} {algo:13s} nb={nb:<3d} {real:>11d} B  {us:10.2f} us  "
+                        tag = f" {env_name}={ev}" if env_name is not None and impl == "pdcc" else ""
+                        print(f"{coll:11s} {impl:5s} {algo:13s} nb={nb:<3d}{tag} {real:>11d} B  {us:10.2f} us  "
                               f"alg {algbw:8.2f}  bus {row['busbw_GBps']:8.2f} GB/s  roof {row['roofline_frac']}"
                               + (f"  graph {graph_us} us" if graph_us is not None else ""),
                               flush=True)
