@@ -41,7 +41,7 @@ struct KArgs {
   int root;
   int redop;
   float scale;
-  int stagger;  // reserved (the staggered-lookahead experiment of round 1; unused by v2)
+  int team_a;   // threads in warp team A: 0 = half the CTA, < 0 = no teams (sequential stages)
 };
 
 struct Geo {
@@ -112,12 +112,14 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
   const uint32_t all = (1u << c.n) - 1u;
   const int T = k.ntiles;
   P p(k, c);
-  const int half = int(blockDim.x) >> 1;
+  // team A gets `half` threads (default: half the CTA), team B the rest; both multiples of 32
+  const bool teams = k.team_a >= 0;
+  const int half = (k.team_a > 0 && k.team_a < int(blockDim.x)) ? (k.team_a & ~31) : int(blockDim.x) >> 1;
   const bool team_a = int(threadIdx.x) < half;
   const bool flag_thread = int(threadIdx.x) < c.n;
   auto whole = [&] { c.tid = threadIdx.x; c.nt = blockDim.x; c.bar = 0; };
   auto split = [&] {
-    c.nt = half;
+    c.nt = team_a ? half : int(blockDim.x) - half;
     c.tid = team_a ? int(threadIdx.x) : int(threadIdx.x) - half;
     c.bar = team_a ? 1 : 2;
   };
@@ -146,7 +148,7 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
     // (2)
     const bool do_in = more && has_in, do_out = has_out && t >= 1;
     const int jobs = int(do_in) + int(has_mid) + int(do_out);
-    if (jobs >= 2) {
+    if (jobs >= 2 && teams) {
       split();
       if (do_in && has_mid) {
         // team A: the local / egress side (push or copy-in of the next tile, then the

@@ -316,7 +316,7 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
   k.ntiles = plan.ntiles;
   k.root = op.root;
   k.redop = redop;
-  k.stagger = env_int("PDCC_STAGGER", 1);
+  k.team_a = env_int("PDCC_TEAM_A", 0);  // A/B knob: threads in team A, -1 = sequential stages
   k.scale = op.scale == 0.0f ? 1.0f : op.scale;
   if (op.redop == PDCC_AVG) k.scale *= 1.0f / float(n);
 
