@@ -254,8 +254,8 @@ def _expected_readers(coll: Collective, n: int):
     return readers
 
 
-def cta(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int, teams: bool = True
-        ) -> Generator[None, None, None]:
+def cta(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int, teams: bool = True,
+        early_ready: bool = False) -> Generator[None, None, None]:
     """One CTA of one rank running one collective call (mirrors run_pipeline / run_ll).
     Yields whenever another CTA may be scheduled; a wait yields until its flags are there."""
     n = machine.n
@@ -334,7 +334,13 @@ def cta(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int, t
         if coll.has_out and t >= 1:
             yield from wait(MID, g, everyone)
         do_in, do_out = more and has_in, has_out and t >= 1
-        a = [run_stage(coll.in_(rank), g + 1)] if do_in else []
+        def in_then_ready():
+            # candidate for round 2: team A publishes READY(t+1) as soon as its own stores are
+            # out, instead of at the end of the iteration (after MID(t) of team B)
+            yield from run_stage(coll.in_(rank), g + 1)
+            post(READY, g + 2, coll.ready_to(rank))
+
+        a = ([in_then_ready()] if early_ready else [run_stage(coll.in_(rank), g + 1)]) if do_in else []
         b = [run_stage(coll.mid(rank), g)] if has_mid else []
         o = [run_stage(coll.out(rank), g - 1)] if do_out else []
         if teams and (len(a) + len(b) + len(o)) >= 2:
@@ -350,7 +356,7 @@ def cta(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int, t
         else:
             for x in a + b + o:
                 yield from x
-        if more:
+        if more and not (early_ready and do_in):
             post(READY, g + 2, coll.ready_to(rank))
         if coll.has_out:
             post(MID, g + 1, everyone)
@@ -369,7 +375,8 @@ def cta(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int, t
 
 
 def run_sequence(n: int, rings: int, calls: List[Tuple[Collective, int, int]], seed: int,
-                 teams: bool = True, max_steps: int = 2_000_000, no_guard: bool = False) -> int:
+                 teams: bool = True, max_steps: int = 2_000_000, no_guard: bool = False,
+                 early_ready: bool = False) -> int:
     """Runs `calls` = [(collective, ntiles, nrings_used)] back to back on every rank with a random
     scheduler. A rank starts call k+1 on a ring as soon as ITS call k on that ring is done (stream
     order), regardless of the other ranks. Returns the number of scheduler steps."""
@@ -392,7 +399,7 @@ def run_sequence(n: int, rings: int, calls: List[Tuple[Collective, int, int]], s
         k = rng.choice(keys)
         if active[k] is None:
             coll, ntiles = queues[k].pop(0)
-            active[k] = cta(m, coll, k[0], k[1], ntiles, teams)
+            active[k] = cta(m, coll, k[0], k[1], ntiles, teams, early_ready)
         before = (dict(m.flag), {kk: (v["tile"], v["writing"], v["reading"]) for kk, v in m.mem.items()})
         try:
             next(active[k])

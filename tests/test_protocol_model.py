@@ -46,3 +46,14 @@ def test_checker_catches_a_missing_slot_guard():
         except pm.ProtocolError:
             caught += 1
     assert caught > 0, "removing the DONE(g - DEPTH) guard must produce a detectable hazard"
+
+
+def test_early_ready_variant_is_also_safe():
+    """Design candidate for round 2: the pushing team posts READY(t+1) right
+    after its own stores, not at the end of the iteration. Checked here before it is built."""
+    n = 4
+    rng = random.Random(11)
+    colls = _collectives(n)
+    for seed in range(8):
+        calls = [(rng.choice(colls), rng.choice([1, 2, 4, 7]), 1) for _ in range(8)]
+        pm.run_sequence(n, 1, calls, seed, early_ready=True)
