@@ -18,17 +18,25 @@ void set_error(const char* fmt, ...) __attribute__((format(printf, 1, 2)));
 //   [0, kCtrlBytes)                 ctrl   local-only bookkeeping (epochs, error record)
 //   [kCtrlBytes, kHeaderBytes)      pads   signal flags written by peers
 //   [kHeaderBytes, +kLLBytes)       LL     kLLRings x PDCC_RING_DEPTH flag-in-data slots
-//   [kDataOffset, +rings)           rings  max_blocks x PDCC_RING_DEPTH tile slots
+//   [kDataOffset, +rings)           rings  max_blocks x ring_bytes; every call cuts its ring
+//                                          into `depth` slots sized for its own tiles
 //   [.., +heap_bytes)               heap   symmetric heap for zero-copy user tensors
 //
 // Every CTA index b owns ring b on every rank: slot(b, pos) sits at the same offset in
 // every rank's block, so one offset addresses "the same tile" on all peers and on the
 // multicast alias. A ring is only ever touched by CTAs with that index, which is what
 // lets per-CTA flag counters order every reuse of a slot across calls.
+// Slot geometry is per call (plan_collective): a call's first `depth` tiles wait until
+// every rank has finished ALL earlier tiles of the ring, so two calls with different slot
+// sizes never overlap inside a ring.
 constexpr size_t kCtrlBytes = 64 * 1024;
 constexpr int kNumChannels = 3;  // READY, MID, DONE
-constexpr size_t kPadBytes =
-    size_t(kNumChannels) * PDCC_MAX_BLOCKS * PDCC_MAX_RANKS * sizeof(uint32_t);
+constexpr size_t kFlagWords = size_t(kNumChannels) * PDCC_MAX_BLOCKS * PDCC_MAX_RANKS;
+// Arrival counters of the zero-copy kernels (multimem.red.add.u32 targets): they sit behind
+// the flag channels inside the pad region, so that every rank can add to every rank's copy
+// through the multicast alias. Word kSymArriveWord + 2*b + phase of the pad region.
+constexpr size_t kSymArriveWord = kFlagWords;
+constexpr size_t kPadBytes = (kFlagWords + 2 * PDCC_MAX_BLOCKS) * sizeof(uint32_t);
 constexpr size_t kHeaderBytes = 2 * 1024 * 1024;  // keeps rings 2 MiB aligned
 static_assert(kCtrlBytes + kPadBytes <= kHeaderBytes, "header too small");
 // LL (low-latency) slots hold {data, flag, data, flag} packets only, never raw payload, so
@@ -44,6 +52,7 @@ constexpr size_t kZeroBytes = kDataOffset;  // what comm creation must clear
 constexpr int kCtrlErr = 0;        // first device-side timeout record: code
 constexpr int kCtrlErrInfo = 1;    // .. chan | tile | peer packed
 constexpr int kCtrlEpoch = 64;     // + b : tiles processed so far by CTA index b
+constexpr int kCtrlSymEpoch = 256;  // + b : zero-copy (symmetric heap) calls made by CTA index b
 
 // What a kernel needs to know about the group, passed by value (88 bytes).
 struct DevComm {
@@ -51,7 +60,7 @@ struct DevComm {
   int nranks;
   char* base[PDCC_MAX_RANKS];  // base[p] = local VA of rank p's symmetric block
   char* mc;                    // multicast alias of the block (nullptr: no NVLS)
-  uint32_t slot_bytes;         // capacity of one tile slot
+  uint32_t ring_bytes;         // bytes of one CTA's ring (cut into slots per call)
   uint32_t timeout_ms;         // device-side wait budget
 };
 
@@ -69,6 +78,8 @@ struct Plan {
   int threads;
   uint64_t tile_bytes;  // payload bytes per CTA per tile (see kernels.cuh)
   int ntiles;
+  int depth;             // slots the ring is cut into for this call
+  uint32_t slot_stride;  // bytes between consecutive slots of a ring
 };
 
 // launch.cu
@@ -81,5 +92,11 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
 int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ranks,
                       const pdcc_op_t& op, const Plan& plan, void* stream);
 size_t dtype_size(int dtype);
+// Copies `n` per-rank argument records into device memory from KERNEL PARAMETERS (a tiny
+// set-up kernel): nothing on the stream ever reads host memory, so the caller's array may
+// live on the stack and the enqueued work stays valid after the caller returns.
+int upload_rank_args(const RankArgs* host, int n, RankArgs* dev, void* stream);
+// True when (dtype, redop) has an all_reduce kernel (P2P variants).
+bool reduce_supported(int dtype, int redop);
 
 }  // namespace pdcc

@@ -155,14 +155,18 @@ struct Ctx {
   uint32_t* ctrl;
   uint64_t deadline;  // globaltimer value after which waits give up
   int* poisoned;      // smem: a wait already timed out in this CTA
-  // The team this thread currently works in. Stage code strides its loops by (tid, nt) and
-  // synchronises on named barrier `bar`; run_pipeline() splits the CTA into two teams so
-  // that the push of tile t+1 and the combine/copy-out of tile t run at the same time.
+  // Slot geometry of this call: the ring of CTA b is cut into `depth` slots of `slot_stride`
+  // bytes; tile t of the call lives in slot t % depth.
+  size_t ring_off;
+  uint32_t slot_stride;
+  int depth;
+  // The warp group this thread works in (run_pipeline gives every pipeline stage its own
+  // group). Stage code strides its loops by (tid, nt); group-wide synchronisation uses the
+  // named barrier `bar`.
   int tid, nt, bar;
 
-  __device__ __forceinline__ size_t slot_off(uint32_t g) const {
-    return kDataOffset +
-           (size_t(b) * PDCC_RING_DEPTH + (g % PDCC_RING_DEPTH)) * a->comm.slot_bytes;
+  __device__ __forceinline__ size_t slot_off(int t) const {
+    return ring_off + size_t(t % depth) * slot_stride;
   }
   __device__ __forceinline__ size_t ll_off(uint32_t g) const {
     return kHeaderBytes + (size_t(b) * PDCC_RING_DEPTH + (g % PDCC_RING_DEPTH)) * kLLSlotBytes;
@@ -172,9 +176,8 @@ struct Ctx {
   __device__ __forceinline__ char* mc(size_t off) const { return a->comm.mc + off; }
 };
 
-// Named-barrier sync of the current team. Not used by the shipped stages (they are
-// barrier-free by construction); kept for stages that may need an intra-team hand-off.
-__device__ __forceinline__ void team_sync(const Ctx& c) {
+// Named-barrier sync of the current warp group (all of its c.nt threads call).
+__device__ __forceinline__ void group_sync(const Ctx& c) {
   asm volatile("bar.sync %0, %1;" ::"r"(c.bar), "r"(c.nt) : "memory");
 }
 
@@ -182,84 +185,97 @@ __device__ __forceinline__ int flag_index(int chan, int b, int src) {
   return (chan * PDCC_MAX_BLOCKS + b) * PDCC_MAX_RANKS + src;
 }
 
-// All threads call. Publishes everything this CTA wrote (locally, to peers, or through
-// the multicast alias) and then raises flag[chan][b][my rank] = val on every rank in mask.
-// bar.sync orders the other threads' writes before thread t's release (cumulativity).
-__device__ __forceinline__ void signal(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
-  __syncthreads();
-  const int t = threadIdx.x;
-  if (t < c.n && ((mask >> t) & 1u)) {
-    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
-    st_release_sys(pad + flag_index(chan, c.b, c.rank), val);
-  }
-}
-
 __device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
-
-// DONE(g) publishes no data: it only says "I no longer touch ring position g % DEPTH", and
-// every access it covers has already returned its value to this CTA (a load whose result
-// was consumed) or is ordered behind it per address. A relaxed store after bar.sync is
-// enough and keeps a system fence off the tail of every tile.
-__device__ __forceinline__ void signal_relaxed(const Ctx& c, int chan, uint32_t val,
-                                               uint32_t mask) {
-  __syncthreads();
-  const int t = threadIdx.x;
-  if (t < c.n && ((mask >> t) & 1u)) {
-    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
-    st_relaxed_sys(pad + flag_index(chan, c.b, c.rank), val);
-  }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// One store that the switch replicates into every rank's pad (the flag word of (chan, b,
+// my rank) has exactly one writer, so a store is enough; no atomic needed).
+__device__ __forceinline__ void multimem_st_u32(uint32_t* mc, uint32_t v) {
+  asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
+}
+// One-instruction arrive on a counter that exists in every rank's block (K8).
+__device__ __forceinline__ void multimem_red_add_u32(uint32_t* mc, uint32_t v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.u32 [%0], %1;" ::"l"(mc), "r"(v) : "memory");
 }
 
-// Building blocks of the fused per-tile flag round in run_pipeline(): thread t (< nranks)
-// polls / posts rank t's flag; fences and CTA barriers are the caller's.
-__device__ __forceinline__ void spin_flag(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
-  const int t = threadIdx.x;
-  if (t < c.n && ((mask >> t) & 1u) && !*c.poisoned) {
-    const uint32_t* f = c.my_pad + flag_index(chan, c.b, t);
-    uint32_t spins = 0;
-    while (static_cast<int32_t>(ld_relaxed_sys(f) - val) < 0) {
-      if ((++spins & 0x3ffu) == 0 && globaltimer_ns() > c.deadline) {
-        if (atomicCAS(c.ctrl + kCtrlErr, 0u, 1u) == 0u)
-          c.ctrl[kCtrlErrInfo] = (uint32_t(chan) << 28) | (uint32_t(t) << 24) | (val & 0xffffffu);
-        *c.poisoned = 1;
-        break;
+__device__ __forceinline__ void record_timeout(const Ctx& c, uint32_t code, uint32_t info) {
+  if (atomicCAS(c.ctrl + kCtrlErr, 0u, code) == 0u) c.ctrl[kCtrlErrInfo] = info;
+  *reinterpret_cast<volatile int*>(c.poisoned) = 1;
+}
+
+// Polls flag[chan][b][src] in MY pad until it reaches val (wrap-safe compare). Returns when
+// it has, when the wall-clock budget is spent (error recorded, CTA poisoned) or when another
+// group of this CTA has already been poisoned: a mismatched collective never hangs the GPU
+// (SURVEY.md §5.2 / §7.3 item 9).
+__device__ __forceinline__ void spin_until(const Ctx& c, int chan, int src, uint32_t val) {
+  const uint32_t* f = c.my_pad + flag_index(chan, c.b, src);
+  uint32_t spins = 0;
+  while (static_cast<int32_t>(ld_relaxed_sys(f) - val) < 0) {
+    if ((++spins & 0x3ffu) == 0) {
+      if (*reinterpret_cast<volatile int*>(c.poisoned)) return;
+      if (globaltimer_ns() > c.deadline) {
+        record_timeout(c, 1u, (uint32_t(chan) << 28) | (uint32_t(src) << 24) | (val & 0xffffffu));
+        return;
       }
     }
   }
 }
-__device__ __forceinline__ void post_flag(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
-  const int t = threadIdx.x;
-  if (t < c.n && ((mask >> t) & 1u)) {
-    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
+
+// ---- group-scoped acquire / release, the only synchronisation of the tile pipeline -----
+//
+// group_wait: thread i (< nranks) of the group polls rank i's flag, then issues a
+// system-scope fence (flag load + fence = acquire); the group barrier hands the guarantee
+// to every thread of the group. group_post: the group barrier orders every thread's writes
+// before thread i's fence (cumulativity), the fence publishes them at system scope, then
+// the relaxed flag store to rank i's pad completes the release. Both follow the PTX memory
+// model to the letter; nothing relies on control dependencies or on store ordering that the
+// model does not promise.
+__device__ __forceinline__ void group_wait(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+  if (c.tid < c.n && ((mask >> c.tid) & 1u)) {
+    if (!*reinterpret_cast<volatile int*>(c.poisoned)) spin_until(c, chan, c.tid, val);
+    fence_acq_rel_sys();
+  }
+  group_sync(c);
+}
+__device__ __forceinline__ void group_post(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+  group_sync(c);
+  if (c.tid < c.n && ((mask >> c.tid) & 1u)) {
+    fence_acq_rel_sys();
+    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[c.tid] + kCtrlBytes);
     st_relaxed_sys(pad + flag_index(chan, c.b, c.rank), val);
   }
 }
 
-// All threads call. Thread t waits for rank t's flag to reach val (wrap-safe), then a
-// system-scope fence makes it an acquire; bar.sync hands the guarantee to the whole CTA.
-// A wait that outlives the budget records an error and poisons the CTA instead of
-// hanging the GPU.
-template <bool ACQUIRE = true>
-__device__ __forceinline__ void wait(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+// ---- CTA-wide forms used by the LL kernels (one unit per thread, no warp groups) ---------
+// The slot guard is an acquire load per polled flag, DONE is a release store: the LL data
+// path itself needs neither (the flag travels inside the data), these only order the reuse
+// of an LL slot PDCC_RING_DEPTH tiles later.
+__device__ __forceinline__ void wait_done_cta(const Ctx& c, uint32_t val, uint32_t mask) {
   const int t = threadIdx.x;
   if (t < c.n && ((mask >> t) & 1u) && !*c.poisoned) {
-    const uint32_t* f = c.my_pad + flag_index(chan, c.b, t);
+    const uint32_t* f = c.my_pad + flag_index(CH_DONE, c.b, t);
     uint32_t spins = 0;
-    while (static_cast<int32_t>(ld_relaxed_sys(f) - val) < 0) {
+    while (static_cast<int32_t>(ld_acquire_sys(f) - val) < 0) {
       if ((++spins & 0x3ffu) == 0 && globaltimer_ns() > c.deadline) {
-        if (atomicCAS(c.ctrl + kCtrlErr, 0u, 1u) == 0u)
-          c.ctrl[kCtrlErrInfo] = (uint32_t(chan) << 28) | (uint32_t(t) << 24) | (val & 0xffffffu);
-        *c.poisoned = 1;
+        record_timeout(c, 1u, (uint32_t(CH_DONE) << 28) | (uint32_t(t) << 24) | (val & 0xffffffu));
         break;
       }
     }
-    // The slot guard (ACQUIRE = false) only orders this CTA's later *writes* after the
-    // peers' completed reads; the control dependency on the flag does that without a fence.
-    if constexpr (ACQUIRE) fence_acq_rel_sys();
   }
   __syncthreads();
+}
+__device__ __forceinline__ void post_done_cta(const Ctx& c, uint32_t val, uint32_t mask) {
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < c.n && ((mask >> t) & 1u)) {
+    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[t] + kCtrlBytes);
+    st_release_sys(pad + flag_index(CH_DONE, c.b, c.rank), val);
+  }
 }
 
 // ---------------------------------------------------------------- copies -------------

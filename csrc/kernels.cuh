@@ -1,21 +1,26 @@
 // K1-K7, K9 — the collectives, written as policies over ONE tile pipeline.
 //
 // Execution model. A call is cut into tiles; CTA b of every rank owns
-// ring b (PDCC_RING_DEPTH slots at the same offset in every rank's symmetric block) and
-// processes tile t of the call as global tile g = g0 + t of that ring, where g0 is the
-// ring's lifetime tile count. Per tile a rank runs up to three stages and raises one
-// monotonic flag per stage on its peers:
+// ring b (the same offset in every rank's symmetric block, cut into `depth` slots for this
+// call) and processes tile t of the call as global tile g = g0 + t of that ring, where g0
+// is the ring's lifetime tile count. A tile passes through up to three stages and every
+// stage raises one monotonic flag on the peers that consume it:
 //
 //   IN   user tensor -> slot(s): pushed to peers, or copied locally   -> READY(g)
-//   MID  wait READY; combine / re-send / copy-out                     -> MID(g)  [two-shot]
+//   MID  wait READY; combine / re-send / copy-out                     -> MID(g)  [3-stage]
 //   OUT  wait MID;   slot -> user tensor                              -> DONE(g)
 //
-// and before touching ring position g % DEPTH again every rank waits for DONE(g-DEPTH)
-// from all ranks. Because the counters never reset and every collective obeys the same
-// slot discipline, consecutive calls of *different* collectives pipeline into each other
-// with no end-of-kernel barrier and no host-side epoch (so launches are graph-capturable).
-// run_pipeline() runs IN(t+1)/OUT(t-1) and MID(t) side by side on two warp teams with one
-// flag round per tile.
+// and before touching slot t % depth again a rank waits for DONE(t - depth) from all
+// ranks. Counters never reset and every collective obeys the same slot discipline, so
+// consecutive calls of different collectives follow each other with no end-of-kernel
+// barrier and no host-side epoch (launches are CUDA-graph capturable).
+//
+// run_pipeline() gives every stage its OWN group of warps and lets the three groups run
+// their tile loops independently: the only coupling between stages — on this rank and
+// across ranks alike — is the flags. While one group sits in the system-scope fence that
+// publishes its tile, the other two keep the links and HBM busy; IN runs up to `depth`
+// tiles ahead of OUT. Tiles are small (tens of KB per CTA) and rings are deep, so a
+// 256 MiB message is ~30-60 tiles per CTA and the pipeline fill is a few percent.
 //
 // Reference parity: one kernel per torch.distributed call site of main.py (lines cited
 // at each policy). The reference itself has no kernels.
@@ -25,11 +30,8 @@
 
 namespace pdcc {
 
-constexpr int kThreads = 512;
-#ifndef PDCC_MIN_CTAS_PER_SM
-#define PDCC_MIN_CTAS_PER_SM 1
-#endif
-constexpr int kMinCtasPerSm = PDCC_MIN_CTAS_PER_SM;
+constexpr int kThreads = 512;     // LL kernels: one 16-byte unit per thread
+constexpr int kMaxThreads = 512;  // pipeline kernels: 16 warps shared by the stage groups (128 regs each)
 
 struct KArgs {
   RankArgs r;           // this rank's view (real multi-GPU launch)
@@ -37,11 +39,11 @@ struct KArgs {
   uint64_t bytes;       // message bytes per tensor (per list element for list ops)
   uint64_t tile_bytes;  // payload bytes per CTA per tile
   uint32_t stride;      // gather / all_gather-push: bytes between per-rank sub-slots
+  uint32_t slot_stride; // bytes between the slots of a ring (this call's geometry)
+  int depth;            // slots per ring
   int ntiles;
   int root;
-  int redop;
   float scale;
-  int team_a;   // threads in warp team A: 0 = half the CTA, < 0 = no teams (sequential stages)
 };
 
 struct Geo {
@@ -81,6 +83,9 @@ __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
   c.tid = threadIdx.x;
   c.nt = blockDim.x;
   c.bar = 0;
+  c.ring_off = kDataOffset + size_t(c.b) * a->comm.ring_bytes;
+  c.slot_stride = k.slot_stride;
+  c.depth = k.depth > 0 ? k.depth : 1;
   c.my_pad = reinterpret_cast<uint32_t*>(a->comm.base[c.rank] + kCtrlBytes);
   c.ctrl = reinterpret_cast<uint32_t*>(a->comm.base[c.rank]);
   c.poisoned = &sh.poison;
@@ -93,107 +98,105 @@ __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
   c.g0 = sh.g0;
 }
 
-// One flag round per tile. Iteration t
-//   (1) waits for everything it is about to consume: the slot of tile t+1 being free
-//       (DONE of tile t+1-DEPTH), READY(t), and MID(t-1) when there is an OUT stage;
-//   (2) runs IN(t+1) + OUT(t-1) and MID(t) AT THE SAME TIME on two teams of warps — the
-//       push (or copy-in) of the next tile and the copy-out of the previous one overlap the
-//       combine / re-send of the current one, so the stages that load different links (or
-//       HBM) never idle each other, even when all CTAs of all ranks run in lockstep;
-//   (3) publishes READY(t+1), MID(t) and DONE with ONE system fence.
-// A rank that has only one kind of work in a collective (the root of a scatter only pushes,
-// the others only copy out) keeps all its threads on it.
+// Warps per stage from the policy's relative weights. A stage with no work on this rank
+// (weight 0) keeps one warp that only forwards its flag, so the flag chain IN -> MID -> OUT
+// -> slot-free is the same on every rank whatever its role.
+__device__ __forceinline__ void split_warps(int nwarps, int nstages, const int* w, int* a) {
+  int idle = 0, tot = 0;
+  for (int i = 0; i < nstages; ++i) {
+    if (w[i] <= 0) ++idle;
+    else tot += w[i];
+  }
+  const int avail = nwarps - idle;
+  int used = 0, last = -1;
+  for (int i = 0; i < 3; ++i) {
+    if (i >= nstages) a[i] = 0;
+    else if (w[i] <= 0) a[i] = 1;
+    else {
+      a[i] = avail * w[i] / tot;
+      if (a[i] < 1) a[i] = 1;
+      used += a[i];
+      last = i;
+    }
+  }
+  if (last >= 0 && avail > used) a[last] += avail - used;
+}
+
+// The tile pipeline: three (two when the policy has no OUT stage) warp groups, each running
+//   for t in tiles:  wait for what the stage consumes; do the stage; publish its flag
+// on its own. Dependencies, per tile t (g = g0 + t):
+//   IN(t)   after DONE(t - depth) from all ranks   (first `depth` tiles: after every rank
+//           finished everything that came before this call on this ring)
+//   MID(t)  after READY(g+1) from the ranks that feed me
+//   OUT(t)  after MID(g+1) from all ranks
+// DONE(g+1) is raised by the last stage. IN(t) of every rank precedes READY, which
+// precedes every MID(t) that writes into peers' slots, so the guard taken by IN also
+// covers the slot writes of MID.
+//
+// Each stage loop is its own __noinline__ function: the three loops never share live
+// registers, so each gets a full allocation and none of them spills.
+template <class P, int STAGE>
+__device__ __noinline__ void stage_loop(const KArgs* kp, Ctx c, bool work) {
+  const KArgs& k = *kp;
+  const uint32_t all = (1u << c.n) - 1u;
+  const int T = k.ntiles;
+  const uint32_t g0 = c.g0;
+  P p(k, c);
+  if constexpr (STAGE == 0) {
+    const uint32_t to = p.ready_to();
+    for (int t = 0; t < T; ++t) {
+      const uint32_t need = t < c.depth ? g0 : g0 + uint32_t(t - c.depth) + 1u;
+      group_wait(c, CH_DONE, need, all);
+      if (work) p.in(t);
+      group_post(c, CH_READY, g0 + uint32_t(t) + 1u, to);
+    }
+  } else if constexpr (STAGE == 1) {
+    const uint32_t from = p.ready_from();
+    for (int t = 0; t < T; ++t) {
+      group_wait(c, CH_READY, g0 + uint32_t(t) + 1u, from);
+      if (work) p.mid(t);
+      group_post(c, P::kHasOut ? CH_MID : CH_DONE, g0 + uint32_t(t) + 1u, all);
+    }
+    if (!P::kHasOut && c.tid == 0) c.ctrl[kCtrlEpoch + c.b] = g0 + uint32_t(T);
+  } else {
+    for (int t = 0; t < T; ++t) {
+      group_wait(c, CH_MID, g0 + uint32_t(t) + 1u, all);
+      if (work) p.out(t);
+      group_post(c, CH_DONE, g0 + uint32_t(t) + 1u, all);
+    }
+    if (c.tid == 0) c.ctrl[kCtrlEpoch + c.b] = g0 + uint32_t(T);
+  }
+}
+
 template <class P>
 __device__ __forceinline__ void run_pipeline(const KArgs& k) {
   __shared__ Prologue sh;
   Ctx c;
   init_ctx(k, sh, c);
 
-  const uint32_t all = (1u << c.n) - 1u;
-  const int T = k.ntiles;
-  P p(k, c);
-  // team A gets `half` threads (default: half the CTA), team B the rest; both multiples of 32
-  const bool teams = k.team_a >= 0;
-  const int half = (k.team_a > 0 && k.team_a < int(blockDim.x)) ? (k.team_a & ~31) : int(blockDim.x) >> 1;
-  const bool team_a = int(threadIdx.x) < half;
-  const bool flag_thread = int(threadIdx.x) < c.n;
-  auto whole = [&] { c.tid = threadIdx.x; c.nt = blockDim.x; c.bar = 0; };
-  auto split = [&] {
-    c.nt = team_a ? half : int(blockDim.x) - half;
-    c.tid = team_a ? int(threadIdx.x) : int(threadIdx.x) - half;
-    c.bar = team_a ? 1 : 2;
-  };
-  const bool has_in = p.has_in(), has_mid = p.has_mid(), has_out = P::kHasOut && p.has_out();
-
-  // prologue: tile 0 enters the pipeline. Flags start at 0 and the compare is wrap-safe,
-  // so the first DEPTH tiles of a ring pass the slot guard immediately.
-  spin_flag(c, CH_DONE, c.g0 - PDCC_RING_DEPTH + 1u, all);
-  __syncthreads();
-  if (has_in) p.in(0);
-  __syncthreads();
-  if (flag_thread) {
-    fence_acq_rel_sys();
-    post_flag(c, CH_READY, c.g0 + 1u, p.ready_to());
+  constexpr int NS = P::kHasOut ? 3 : 2;
+  int w[3] = {0, 0, 0};
+  {
+    P p(k, c);
+    w[0] = p.w_in();
+    w[1] = p.w_mid();
+    if constexpr (P::kHasOut) w[2] = p.w_out();
   }
-
-  for (int t = 0; t < T; ++t) {
-    const uint32_t g = c.g0 + uint32_t(t);
-    const bool more = t + 1 < T;
-    // (1)
-    if (more) spin_flag(c, CH_DONE, g + 1u - PDCC_RING_DEPTH + 1u, all);
-    spin_flag(c, CH_READY, g + 1u, p.ready_from());
-    if (P::kHasOut && t >= 1) spin_flag(c, CH_MID, g, all);
-    if (flag_thread) fence_acq_rel_sys();
-    __syncthreads();
-    // (2)
-    const bool do_in = more && has_in, do_out = has_out && t >= 1;
-    const int jobs = int(do_in) + int(has_mid) + int(do_out);
-    if (jobs >= 2 && teams) {
-      split();
-      if (do_in && has_mid) {
-        // team A: the local / egress side (push or copy-in of the next tile, then the
-        // copy-out of the previous one); team B: the combine / re-send of the current tile
-        if (team_a) {
-          p.in(t + 1);
-          if (do_out) p.out(t - 1);
-        } else {
-          p.mid(t);
-        }
-      } else if (do_in) {  // no MID on this rank (root of a rooted reduce): push vs copy-out
-        if (team_a) p.in(t + 1);
-        else p.out(t - 1);
-      } else {  // no IN on this rank: re-send and copy-out side by side
-        if (team_a) p.out(t - 1);
-        else p.mid(t);
-      }
-      whole();
-    } else {
-      if (do_in) p.in(t + 1);
-      if (has_mid) p.mid(t);
-      if (do_out) p.out(t - 1);
-    }
-    // (3)
-    __syncthreads();
-    if (flag_thread) {
-      fence_acq_rel_sys();
-      if (more) post_flag(c, CH_READY, g + 2u, p.ready_to());
-      if constexpr (P::kHasOut) {
-        post_flag(c, CH_MID, g + 1u, all);
-        if (t >= 1) post_flag(c, CH_DONE, g, all);
-      } else {
-        post_flag(c, CH_DONE, g + 1u, all);
-      }
-    }
-  }
-  if constexpr (P::kHasOut) {
-    spin_flag(c, CH_MID, c.g0 + uint32_t(T), all);
-    if (flag_thread) fence_acq_rel_sys();
-    __syncthreads();
-    if (has_out) p.out(T - 1);
-    __syncthreads();
-    post_flag(c, CH_DONE, c.g0 + uint32_t(T), all);
-  }
-  if (threadIdx.x == 0) c.ctrl[kCtrlEpoch + c.b] = c.g0 + uint32_t(T);
+  int a[3];
+  split_warps(int(blockDim.x) >> 5, NS, w, a);
+  const int warp = int(threadIdx.x) >> 5;
+  int stage, first;
+  if (warp < a[0]) { stage = 0; first = 0; }
+  else if (warp < a[0] + a[1]) { stage = 1; first = a[0]; }
+  else if (warp < a[0] + a[1] + a[2]) { stage = 2; first = a[0] + a[1]; }
+  else return;  // warps beyond the groups (a collective with no work on this rank) leave
+  c.tid = int(threadIdx.x) - first * 32;
+  c.nt = a[stage] * 32;
+  c.bar = 1 + stage;
+  const bool work = w[stage] > 0;
+  if (stage == 0) stage_loop<P, 0>(&k, c, work);
+  else if (stage == 1) stage_loop<P, 1>(&k, c, work);
+  else if constexpr (P::kHasOut) stage_loop<P, 2>(&k, c, work);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -238,7 +241,7 @@ __device__ __forceinline__ void store_user_unit(char* base, uint64_t len, size_t
 // whose length is a multiple of 16 streams through the unrolled vector loops; a ragged
 // tail or an odd view is assembled byte-exactly, one unit per thread, and stored as whole
 // 16-byte units all the same (slots have room). No staging and no barrier either way, so
-// the two warp teams of run_pipeline() never have to synchronise inside a stage.
+// the warp groups of run_pipeline() never have to synchronise inside a stage.
 template <bool MC>
 __device__ __forceinline__ void push_user(const Ctx& c, const char* src, uint64_t len,
                                           size_t dst_off, size_t /*stage_off*/, uint32_t mask) {
@@ -408,17 +411,18 @@ struct ReducePolicy {
   __device__ __forceinline__ uint32_t ready_from() const {
     return (ROOTED && !kTwoShot) ? (c.rank == k.root ? all : 0u) : all;
   }
-  // which stages have work on THIS rank (uniform across the CTA)
-  __device__ __forceinline__ bool has_in() const {
-    return !(ROOTED && ALGO == AR_ONESHOT_P2P && c.rank == k.root);
+  // Relative weight of each stage on THIS rank (uniform across the CTA); run_pipeline()
+  // sizes the warp groups from these. 0 = the stage has no work here.
+  __device__ __forceinline__ int w_in() const {
+    return (ROOTED && ALGO == AR_ONESHOT_P2P && c.rank == k.root) ? 0 : 1;
   }
-  __device__ __forceinline__ bool has_mid() const {
-    if constexpr (!ROOTED) return true;
-    else if constexpr (ALGO == AR_TWOSHOT_P2P) return c.rank != k.root;  // owners
-    else if constexpr (ALGO == AR_TWOSHOT_NVLS) return true;
-    else return c.rank == k.root;
+  __device__ __forceinline__ int w_mid() const {
+    if constexpr (!ROOTED) return ALGO == AR_ONESHOT_NVLS ? 2 : 1;
+    else if constexpr (ALGO == AR_TWOSHOT_P2P) return c.rank != k.root ? 1 : 0;  // owners
+    else if constexpr (ALGO == AR_TWOSHOT_NVLS) return 1;
+    else return c.rank == k.root ? (ALGO == AR_ONESHOT_NVLS ? 3 : 1) : 0;
   }
-  __device__ __forceinline__ bool has_out() const { return !ROOTED || c.rank == k.root; }
+  __device__ __forceinline__ int w_out() const { return (!ROOTED || c.rank == k.root) ? 1 : 0; }
   // Two-shot P2P ownership. all_reduce: every rank owns one chunk of the tile. Rooted
   // reduce: only the n-1 NON-root ranks own chunks, so the root receives each reduced
   // chunk exactly once and nothing else: S bytes in, S bytes out on every GPU, instead of
@@ -445,7 +449,7 @@ struct ReducePolicy {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    const size_t so = c.slot_off(c.g0 + t);
+    const size_t so = c.slot_off(t);
     const char* src = static_cast<const char*>(c.a->in) + off;
     if constexpr (kNvls) {
       copy_bytes<LD_USER, 8>(c, c.mine(so), src, len);
@@ -570,7 +574,7 @@ struct ReducePolicy {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    const size_t so = c.slot_off(c.g0 + t);
+    const size_t so = c.slot_off(t);
     const size_t n16 = (len + 15) >> 4;
     const size_t nelem = len / sizeof(T);
     const size_t elem0 = off / sizeof(T);
@@ -626,7 +630,7 @@ struct ReducePolicy {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    const size_t so = c.slot_off(c.g0 + t);
+    const size_t so = c.slot_off(t);
     if constexpr (ALGO == AR_TWOSHOT_P2P) {
       if (ROOTED && c.rank != k.root) return;
       const size_t sub = sub_bytes();
@@ -643,22 +647,11 @@ struct ReducePolicy {
   }
 };
 
-template <typename T, bool WIDE, int ALGO, bool ROOTED>
-__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) reduce_kernel(const __grid_constant__ KArgs k) {
-  switch (k.redop) {
-    case PDCC_SUM:
-      run_pipeline<ReducePolicy<T, WIDE, PDCC_SUM, ALGO, ROOTED>>(k);
-      break;
-    case PDCC_PRODUCT:
-      run_pipeline<ReducePolicy<T, WIDE, PDCC_PRODUCT, ALGO, ROOTED>>(k);
-      break;
-    case PDCC_MIN:
-      run_pipeline<ReducePolicy<T, WIDE, PDCC_MIN, ALGO, ROOTED>>(k);
-      break;
-    default:
-      run_pipeline<ReducePolicy<T, WIDE, PDCC_MAX, ALGO, ROOTED>>(k);
-      break;
-  }
+// The ReduceOp is a template parameter (chosen on the host, launch.cu) so that every kernel
+// carries exactly one combine: no four-way switch around the pipeline, no register spills.
+template <typename T, bool WIDE, int OP, int ALGO, bool ROOTED>
+__global__ void __launch_bounds__(kMaxThreads, 1) reduce_kernel(const __grid_constant__ KArgs k) {
+  run_pipeline<ReducePolicy<T, WIDE, OP, ALGO, ROOTED>>(k);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -717,17 +710,19 @@ struct MovePolicy {
     else return all;
   }
 
-  // which stages have work on THIS rank (uniform across the CTA)
-  __device__ __forceinline__ bool has_in() const {
-    if constexpr (kTwoPhase || kRootSends) return c.rank == k.root;
-    else return KIND != MV_BARRIER;
+  // relative weight of each stage on THIS rank (0 = no work here), see run_pipeline()
+  __device__ __forceinline__ int w_in() const {
+    if constexpr (kTwoPhase || kRootSends) return c.rank == k.root ? 1 : 0;
+    else return KIND != MV_BARRIER ? 1 : 0;
   }
-  __device__ __forceinline__ bool has_mid() const {
-    if constexpr (kTwoPhase || kRootSends) return c.rank != k.root;
-    else if constexpr (KIND == MV_GATHER) return c.rank == k.root;
-    else return KIND != MV_BARRIER;
+  __device__ __forceinline__ int w_mid() const {
+    if constexpr (kTwoPhase || kRootSends) return c.rank != k.root ? 1 : 0;
+    else if constexpr (KIND == MV_GATHER) return c.rank == k.root ? 3 : 0;
+    else if constexpr (KIND == MV_ALLGATHER_PULL) return 3;
+    else if constexpr (KIND == MV_ALLGATHER_NVLS) return 2;
+    else return KIND != MV_BARRIER ? 1 : 0;
   }
-  __device__ __forceinline__ bool has_out() const { return kTwoPhase && c.rank != k.root; }
+  __device__ __forceinline__ int w_out() const { return (kTwoPhase && c.rank != k.root) ? 1 : 0; }
 
   template <bool MC>
   __device__ __forceinline__ void push(const char* src, uint64_t len, size_t dst_off,
@@ -739,7 +734,7 @@ struct MovePolicy {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    const size_t so = c.slot_off(c.g0 + t);
+    const size_t so = c.slot_off(t);
     if constexpr (KIND == MV_BROADCAST_P2P || KIND == MV_BROADCAST_NVLS) {
       if (c.rank != k.root) return;
       const char* src = static_cast<const char*>(c.a->in) + off;
@@ -790,7 +785,7 @@ struct MovePolicy {
     uint64_t off, len;
     geo.range(t, off, len);
     if (len == 0) return;
-    const size_t so = c.slot_off(c.g0 + t);
+    const size_t so = c.slot_off(t);
     if constexpr (KIND == MV_BROADCAST_P2P || KIND == MV_BROADCAST_NVLS || KIND == MV_SCATTER) {
       if (c.rank == k.root) return;
       copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->out) + off, c.mine(so), len);
@@ -835,20 +830,20 @@ struct MovePolicy {
       uint64_t off, len;
       geo.range(t, off, len);
       if (len == 0) return;
-      copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->out) + off, c.mine(c.slot_off(c.g0 + t)), len);
+      copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->out) + off, c.mine(c.slot_off(t)), len);
     }
   }
 };
 
 template <int KIND>
-__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) move_kernel(const __grid_constant__ KArgs k) {
+__global__ void __launch_bounds__(kMaxThreads, 1) move_kernel(const __grid_constant__ KArgs k) {
   run_pipeline<MovePolicy<KIND>>(k);
 }
 
 // per-dtype launch tables, one translation unit each (kern_<dtype>.cu)
 typedef void (*KernelFn)(KArgs);
-KernelFn reduce_kernel_for(int dtype, bool wide, int ar_algo, bool rooted);
-#define PDCC_DECLARE_REDUCE_TABLE(NAME) KernelFn NAME(bool wide, int ar_algo, bool rooted)
+KernelFn reduce_kernel_for(int dtype, bool wide, int redop, int ar_algo, bool rooted);
+#define PDCC_DECLARE_REDUCE_TABLE(NAME) KernelFn NAME(bool wide, int redop, int ar_algo, bool rooted)
 PDCC_DECLARE_REDUCE_TABLE(reduce_table_f32);
 PDCC_DECLARE_REDUCE_TABLE(reduce_table_bf16);
 PDCC_DECLARE_REDUCE_TABLE(reduce_table_f16);

@@ -6,7 +6,10 @@
 // SURVEY.md §7.1 step 9; profiles/ holds the sweeps they were read from.
 #include <cuda_runtime.h>
 
+#include <string.h>
+
 #include <atomic>
+#include <mutex>
 
 #include "ll.cuh"
 #include "tma_copy.cuh"
@@ -35,15 +38,15 @@ static bool nvls_reducible(int dtype, int redop) {
   }
 }
 
-KernelFn reduce_kernel_for(int dtype, bool wide, int ar_algo, bool rooted) {
+KernelFn reduce_kernel_for(int dtype, bool wide, int redop, int ar_algo, bool rooted) {
   switch (dtype) {
-    case PDCC_F32: return reduce_table_f32(wide, ar_algo, rooted);
-    case PDCC_BF16: return reduce_table_bf16(wide, ar_algo, rooted);
-    case PDCC_F16: return reduce_table_f16(wide, ar_algo, rooted);
-    case PDCC_F64: return reduce_table_f64(wide, ar_algo, rooted);
-    case PDCC_I32: return reduce_table_i32(wide, ar_algo, rooted);
-    case PDCC_I64: return reduce_table_i64(wide, ar_algo, rooted);
-    case PDCC_U8: return reduce_table_u8(wide, ar_algo, rooted);
+    case PDCC_F32: return reduce_table_f32(wide, redop, ar_algo, rooted);
+    case PDCC_BF16: return reduce_table_bf16(wide, redop, ar_algo, rooted);
+    case PDCC_F16: return reduce_table_f16(wide, redop, ar_algo, rooted);
+    case PDCC_F64: return reduce_table_f64(wide, redop, ar_algo, rooted);
+    case PDCC_I32: return reduce_table_i32(wide, redop, ar_algo, rooted);
+    case PDCC_I64: return reduce_table_i64(wide, redop, ar_algo, rooted);
+    case PDCC_U8: return reduce_table_u8(wide, redop, ar_algo, rooted);
     default: return nullptr;
   }
 }
@@ -84,6 +87,57 @@ static int env_int(const char* name, int dflt) {
   return (v && *v) ? atoi(v) : dflt;
 }
 
+// Planner knobs. Read from the environment ONCE (first use) and cached: the planner runs on
+// every collective call and getenv is a linear scan of the environment. pdcc_reload_env()
+// re-reads them (benchmarks A/B a knob inside one job).
+struct PlanEnv {
+  int ll_max;             // PDCC_LL_MAX            bytes; <0 = default (512 KiB / n)
+  int oneshot_p2p_max;    // PDCC_ONESHOT_P2P_MAX   all_reduce one-shot up to this size (n > 2)
+  int nvls_min_ranks;     // PDCC_NVLS_MIN_RANKS    all_reduce uses the switch above this group size
+  int rooted_twoshot_min; // PDCC_ROOTED_TWOSHOT_MIN reduce/broadcast: two-phase from this size
+  int max_ctas;           // PDCC_MAX_CTAS          hard cap on CTAs per call (0 = none)
+  int default_ctas;       // PDCC_DEFAULT_CTAS      cap below 8 MiB (0 = 128; >0 also caps big ones)
+  int tile_bytes;         // PDCC_TILE_BYTES        payload per CTA per tile (0 = table)
+  int depth;              // PDCC_DEPTH             max slots per ring (0 = 8)
+  int threads;            // PDCC_THREADS           threads per CTA of the pipeline kernels (0 = auto)
+  int copy_tma;           // PDCC_COPY_TMA          local copies through the TMA engine (default 1)
+};
+static PlanEnv g_plan_env;
+static std::atomic<int> g_plan_env_state{0};  // 0 = not read, 1 = valid
+
+static void read_plan_env(PlanEnv* e) {
+  e->ll_max = env_int("PDCC_LL_MAX", -1);
+  e->oneshot_p2p_max = env_int("PDCC_ONESHOT_P2P_MAX", 1 << 20);
+  e->nvls_min_ranks = env_int("PDCC_NVLS_MIN_RANKS", 4);
+  e->rooted_twoshot_min = env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20);
+  e->max_ctas = env_int("PDCC_MAX_CTAS", 0);
+  e->default_ctas = env_int("PDCC_DEFAULT_CTAS", 0);
+  e->tile_bytes = env_int("PDCC_TILE_BYTES", 0);
+  e->depth = env_int("PDCC_DEPTH", 0);
+  e->threads = env_int("PDCC_THREADS", 0);
+  e->copy_tma = env_int("PDCC_COPY_TMA", 1);
+}
+
+static const PlanEnv& plan_env() {
+  if (g_plan_env_state.load(std::memory_order_acquire) == 0) {
+    static std::mutex mu;
+    std::lock_guard<std::mutex> g(mu);
+    if (g_plan_env_state.load(std::memory_order_relaxed) == 0) {
+      read_plan_env(&g_plan_env);
+      g_plan_env_state.store(1, std::memory_order_release);
+    }
+  }
+  return g_plan_env;
+}
+
+// Payload bytes per CTA per tile when the caller does not force one (PDCC_TILE_BYTES).
+// Measured table (profiles/): see DESIGN.md §4 "tiles".
+static uint64_t default_tile(int coll, int algo, int n, uint64_t bytes) {
+  (void)coll; (void)algo; (void)n;
+  if (bytes >= (uint64_t(64) << 20)) return 64 << 10;
+  return 32 << 10;
+}
+
 int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc_op_t& op,
                     Plan* plan) {
   const int n = comm.nranks;
@@ -111,7 +165,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   // Small messages: flag-in-data push (ll.cuh). Above the threshold the doubled wire
   // bytes cost more than the fences they save. Thresholds from profiles/ sweeps.
   if (algo == PDCC_ALGO_AUTO && op.coll != PDCC_BARRIER && n > 1 &&
-      bytes <= uint64_t(env_int("PDCC_LL_MAX", (512 << 10) / n)))
+      bytes <= uint64_t(plan_env().ll_max >= 0 ? plan_env().ll_max : (512 << 10) / n))
     algo = PDCC_ALGO_LL;
   if (algo == PDCC_ALGO_LL) {
     if (op.coll == PDCC_BARRIER) {
@@ -126,6 +180,8 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
     plan->threads = kThreads;
     plan->tile_bytes = kLLTileBytes;
     plan->ntiles = int(ceil_div(bytes ? bytes : 1, uint64_t(kLLTileBytes) * nb));
+    plan->depth = PDCC_RING_DEPTH;
+    plan->slot_stride = uint32_t(kLLSlotBytes);
     return PDCC_OK;
   }
   if (op.coll == PDCC_ALL_REDUCE) {
@@ -139,13 +195,13 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       // has one flag round less, so it wins at every size; the switch wins from n = 4 up.
       if (n <= 2) {
         algo = PDCC_ALGO_ONESHOT_P2P;
-      } else if (bytes <= uint64_t(env_int("PDCC_ONESHOT_P2P_MAX", 1 << 20))) {
+      } else if (bytes <= uint64_t(plan_env().oneshot_p2p_max)) {
         // one multimem.ld_reduce per unit instead of n-1 pushed copies: measured at
         // 8 GPUs, 256 KiB: 17.4 us vs 20.7 us (profiles/sweep_n8_v1.jsonl, graph-timed)
-        algo = (nvls && n > env_int("PDCC_NVLS_MIN_RANKS", 4)) ? PDCC_ALGO_ONESHOT_NVLS
+        algo = (nvls && n > plan_env().nvls_min_ranks) ? PDCC_ALGO_ONESHOT_NVLS
                                                                : PDCC_ALGO_ONESHOT_P2P;
       } else {
-        algo = (nvls && n > env_int("PDCC_NVLS_MIN_RANKS", 4)) ? PDCC_ALGO_TWOSHOT_NVLS
+        algo = (nvls && n > plan_env().nvls_min_ranks) ? PDCC_ALGO_TWOSHOT_NVLS
                                                                : PDCC_ALGO_TWOSHOT_P2P;
       }
     }
@@ -169,7 +225,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       // A single GPU pulling everything through multimem.ld_reduce tops out near half the
       // link rate (profiles/). Large messages: two-shot push where only the non-root ranks
       // own chunks: S bytes in and out of every GPU, all of it posted stores.
-      const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
+      const uint64_t big = uint64_t(plan_env().rooted_twoshot_min);
       if (n > 2 && bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
       else if (nvls && n >= 4) algo = PDCC_ALGO_NVLS;
       else algo = PDCC_ALGO_P2P;
@@ -193,7 +249,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
         // One GPU cannot feed the multicast engine (or n-1 peers) at link rate; from a few
         // MB up the root deals shards to the other ranks and they re-send them among
         // themselves (two-phase, unicast stores, S bytes per GPU and direction).
-        const uint64_t big = uint64_t(env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20));
+        const uint64_t big = uint64_t(plan_env().rooted_twoshot_min);
         if (n <= 2) algo = PDCC_ALGO_P2P;
         else if (mc_ok && n <= 4) algo = PDCC_ALGO_NVLS;  // measured: replication to <= 3 peers keeps up
         else if (bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
@@ -225,47 +281,40 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS))
     algo = PDCC_ALGO_P2P;
 
-  // ---- grid + tile ---------------------------------------------------------------
-  // cap: payload one CTA may place in one slot for this collective
-  uint64_t cap = comm.slot_bytes;
-  uint64_t align = 16;
+  // ---- grid + tile + ring geometry -------------------------------------------------
   const bool reduce_coll = op.coll == PDCC_ALL_REDUCE || op.coll == PDCC_REDUCE;
   const bool oneshot_push = reduce_coll && (algo == PDCC_ALGO_ONESHOT_P2P || algo == PDCC_ALGO_P2P);
   const bool twoshot_push = reduce_coll && algo == PDCC_ALGO_TWOSHOT_P2P;
   const bool sub_slots = op.coll == PDCC_GATHER || oneshot_push ||
                          (op.coll == PDCC_ALL_GATHER && algo != PDCC_ALGO_PULL);
-  if (sub_slots) cap = (comm.slot_bytes / n) & ~uint64_t(15);  // one sub-slot per source rank
   const bool bcast_2p = op.coll == PDCC_BROADCAST &&
                         (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS);
   // chunk owners: every rank, or every rank but the root (rooted two-shot push, two-phase
   // broadcast), see ReducePolicy / MovePolicy
   const uint64_t nown = ((twoshot_push && op.coll == PDCC_REDUCE) || bcast_2p) ? uint64_t(n - 1)
                                                                                : uint64_t(n);
-  if (twoshot_push) cap = comm.slot_bytes * nown / (uint64_t(n) + nown);  // n partials + reduced chunks
-  if (twoshot_push || bcast_2p || (reduce_coll && algo == PDCC_ALGO_TWOSHOT_NVLS)) {
+  uint64_t align = 16;
+  if (twoshot_push || bcast_2p || (reduce_coll && algo == PDCC_ALGO_TWOSHOT_NVLS))
     align = 16 * (nown ? nown : 1);
-    cap = cap / align * align;
-  }
-  if (cap < align) {
-    set_error("slot_bytes %u too small for %d ranks", comm.slot_bytes, n);
-    return PDCC_EINVAL;
-  }
+  // payload one CTA may place in one slot of `slot` bytes for this collective
+  auto payload_cap = [&](uint64_t slot) -> uint64_t {
+    uint64_t cap = slot;
+    if (sub_slots) cap = (slot / n) & ~uint64_t(15);                       // one sub-slot per source rank
+    if (twoshot_push) cap = slot * nown / (uint64_t(n) + nown);           // n partials + reduced chunks
+    return cap / align * align;
+  };
 
-  int max_blocks = env_int("PDCC_MAX_CTAS", 0);
+  const PlanEnv& pe = plan_env();
   if (ring_limit <= 0 || ring_limit > PDCC_MAX_BLOCKS) ring_limit = PDCC_MAX_BLOCKS;
-  if (max_blocks <= 0) {
-    // Bandwidth collectives: enough CTAs to keep ~4 MB in flight per GPU; the rooted
-    // movers are limited by one GPU's link so fewer suffice.
-    max_blocks = env_int("PDCC_DEFAULT_CTAS", 128);
-  }
+  int max_blocks = pe.max_ctas > 0 ? pe.max_ctas : (pe.default_ctas > 0 ? pe.default_ctas : 128);
   if (max_blocks > ring_limit) max_blocks = ring_limit;
 
   int nb = op.nblocks;
   if (nb <= 0) {
     const uint64_t per_cta = 32 << 10;  // below this a CTA is latency- not bandwidth-bound
     nb = int(ceil_div(bytes ? bytes : 1, per_cta));
-    // big messages: every SM pushes (NVLink stores are limited per SM, profiles/)
-    if (bytes >= (uint64_t(8) << 20) && env_int("PDCC_DEFAULT_CTAS", 0) <= 0) max_blocks = ring_limit;
+    // big messages: every SM takes part (the stage groups share each SM's warps)
+    if (bytes >= (uint64_t(8) << 20) && pe.max_ctas <= 0 && pe.default_ctas <= 0) max_blocks = ring_limit;
     if (nb > max_blocks) nb = max_blocks;
     if (nb < 1) nb = 1;
   }
@@ -274,29 +323,44 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
     return PDCC_EINVAL;
   }
 
-  uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
-  // Every tile costs one flag round (a system fence that drains the CTA's outstanding
-  // NVLink stores plus the flag's flight, ~5 us), but only neighbouring tiles overlap
-  // their stages (staging copies under the NVLink phase; the two link directions of the
-  // rooted two-phase collectives). Measured on 8xB200 at 256 MiB (profiles/final_n8.md):
-  // all_reduce 972 / 786 us with 1 / 4 tiles per CTA, reduce 745 / 662 / 627 us and
-  // broadcast 775 / 589 / 585 us with 1 / 4 / 8.
-  const bool rooted_two_phase = (twoshot_push && op.coll == PDCC_REDUCE) || bcast_2p;
-  uint64_t split = uint64_t(env_int("PDCC_TILE_SPLIT", 0));
-  if (split == 0) split = rooted_two_phase ? 8 : 4;
-  uint64_t tile = per_cta / split;
-  const uint64_t min_tile = 64 << 10;
-  if (tile < min_tile) tile = per_cta < min_tile ? per_cta : min_tile;
+  // Tile: small enough that a message is tens of tiles per CTA (short pipeline fill) and
+  // that `depth` of them fit in the ring; big enough that the per-tile fence + flag of a
+  // stage group (a few microseconds, overlapped by the other groups) stays cheap.
+  const uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
+  uint64_t want = pe.tile_bytes > 0 ? uint64_t(pe.tile_bytes) : default_tile(op.coll, algo, n, bytes);
+  uint64_t tile = per_cta < want ? per_cta : want;
   tile = round_up(tile, align);
-  if (tile > cap) tile = cap;
+  const int max_depth = pe.depth > 0 ? pe.depth : 8;
+  int depth = 1;
+  uint64_t slot = 0;
+  for (int d = max_depth; d >= 1; d >>= 1) {
+    const uint64_t sl = (uint64_t(comm.ring_bytes) / uint64_t(d)) & ~uint64_t(255);
+    if (payload_cap(sl) >= tile || d == 1) {
+      depth = d;
+      slot = sl;
+      break;
+    }
+  }
+  if (payload_cap(slot) < tile) tile = payload_cap(slot);
+  if (tile < align) {
+    set_error("ring of %u bytes too small for %d ranks", comm.ring_bytes, n);
+    return PDCC_EINVAL;
+  }
   if (op.coll == PDCC_BARRIER) tile = align;
 
   plan->algo = algo;
   plan->nblocks = nb;
-  plan->threads = kThreads;
+  // three-stage collectives share an SM between three warp groups: give them more warps
+  const bool three = (reduce_coll && (algo == PDCC_ALGO_TWOSHOT_P2P || algo == PDCC_ALGO_TWOSHOT_NVLS)) || bcast_2p;
+  plan->threads = pe.threads > 0 ? pe.threads : (three ? kMaxThreads : kThreads);
+  if (plan->threads > kMaxThreads) plan->threads = kMaxThreads;
+  plan->threads = plan->threads / 32 * 32;
+  if (plan->threads < 96) plan->threads = 96;
   plan->tile_bytes = tile;
   plan->ntiles = int(ceil_div(bytes ? bytes : 1, tile * uint64_t(nb)));
   if (plan->ntiles < 1) plan->ntiles = 1;
+  plan->depth = depth;
+  plan->slot_stride = uint32_t(slot);
   return PDCC_OK;
 }
 
@@ -314,9 +378,9 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
   k.tile_bytes = plan.tile_bytes;
   k.stride = uint32_t(round_up(plan.tile_bytes, 16));
   k.ntiles = plan.ntiles;
+  k.depth = plan.depth;
+  k.slot_stride = plan.slot_stride;
   k.root = op.root;
-  k.redop = redop;
-  k.team_a = env_int("PDCC_TEAM_A", 0);  // A/B knob: threads in team A, -1 = sequential stages
   k.scale = op.scale == 0.0f ? 1.0f : op.scale;
   if (op.redop == PDCC_AVG) k.scale *= 1.0f / float(n);
 
@@ -333,7 +397,7 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
         set_error("fused cast supports bf16/f16 -> f32 only");
         return PDCC_EINVAL;
       }
-      fn = reduce_kernel_for(op.dtype, wide,
+      fn = reduce_kernel_for(op.dtype, wide, redop,
                              plan.algo == PDCC_ALGO_LL ? AR_LL : plan.algo - PDCC_ALGO_ONESHOT_P2P,
                              false);
       break;
@@ -343,7 +407,7 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
         set_error("reduce has no fused cast");
         return PDCC_EINVAL;
       }
-      fn = reduce_kernel_for(op.dtype, false,
+      fn = reduce_kernel_for(op.dtype, false, redop,
                              plan.algo == PDCC_ALGO_LL            ? AR_LL
                              : plan.algo == PDCC_ALGO_NVLS        ? AR_ONESHOT_NVLS
                              : plan.algo == PDCC_ALGO_TWOSHOT_P2P ? AR_TWOSHOT_P2P
@@ -402,6 +466,40 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
 }
 
 // ---------------------------------------------------------------------------------------
+// Per-rank arguments of the single-GPU emulation, written to device memory by a kernel that
+// receives them BY VALUE: the launch copies them at enqueue time, so neither a later
+// overwrite of the host array nor a replay of a captured launch can read stale host memory.
+// ---------------------------------------------------------------------------------------
+struct RankArgsPack {
+  RankArgs r[PDCC_MAX_RANKS];
+};
+__global__ void rank_args_kernel(const __grid_constant__ RankArgsPack pack, RankArgs* dst, int n) {
+  constexpr int kWords = int(sizeof(RankArgs) / 4);
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(&pack);
+  uint32_t* d = reinterpret_cast<uint32_t*>(dst);
+  for (int i = threadIdx.x; i < n * kWords; i += blockDim.x) d[i] = src[i];
+}
+
+int upload_rank_args(const RankArgs* host, int n, RankArgs* dev, void* stream) {
+  if (n < 1 || n > PDCC_MAX_RANKS || !host || !dev) return PDCC_EINVAL;
+  RankArgsPack pack;
+  memset(&pack, 0, sizeof(pack));
+  for (int r = 0; r < n; ++r) pack.r[r] = host[r];
+  rank_args_kernel<<<1, 128, 0, static_cast<cudaStream_t>(stream)>>>(pack, dev, n);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("uploading per-rank arguments: %s", cudaGetErrorString(e));
+    return PDCC_ECUDA;
+  }
+  return PDCC_OK;
+}
+
+bool reduce_supported(int dtype, int redop) {
+  return reduce_kernel_for(dtype, false, redop == PDCC_AVG ? PDCC_SUM : redop, AR_ONESHOT_P2P,
+                           false) != nullptr;
+}
+
+// ---------------------------------------------------------------------------------------
 // K9 local helpers: the world-size-1 degenerate collectives (a list op over one rank is a
 // copy) and the DP demo's scale+cast when there is nobody to reduce with.
 // ---------------------------------------------------------------------------------------
@@ -450,6 +548,13 @@ extern "C" {
 
 uint64_t pdcc_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
+void pdcc_reload_env(void) {
+  PlanEnv e;
+  read_plan_env(&e);
+  (void)plan_env();
+  g_plan_env = e;
+}
+
 static int set_device_checked(int device) {
   if (device < 0) return PDCC_OK;
   cudaError_t e = cudaSetDevice(device);
@@ -467,7 +572,7 @@ int pdcc_local_copy(void* dst, const void* src, uint64_t bytes, int device, void
   if (rc) return rc;
   cudaError_t e;
   const bool tma_ok = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src) | bytes) & 15u) == 0 &&
-                      bytes >= (uint64_t(1) << 20) && env_int("PDCC_COPY_TMA", 1) != 0;
+                      bytes >= (uint64_t(1) << 20) && plan_env().copy_tma != 0;
   if (tma_ok) {
     // big aligned copies go through the TMA engine (tma_copy.cuh), two CTAs per SM
     static bool attr_set[64] = {};

@@ -160,26 +160,20 @@ __device__ __forceinline__ void run_ll(const KArgs& k) {
   const uint32_t all = (1u << c.n) - 1u;
   for (int t = 0; t < k.ntiles; ++t) {
     const uint32_t g = c.g0 + uint32_t(t);
-    wait<false>(c, CH_DONE, g - PDCC_RING_DEPTH + 1u, all);  // slot guard, as everywhere
+    wait_done_cta(c, g - PDCC_RING_DEPTH + 1u, all);  // LL slot g % DEPTH is free again
     ll_tile<KIND, T, OP, WIDE>(k, c, t);
-    signal_relaxed(c, CH_DONE, g + 1u, all);
+    post_done_cta(c, g + 1u, all);
   }
   if (threadIdx.x == 0) c.ctrl[kCtrlEpoch + c.b] = c.g0 + uint32_t(k.ntiles);
 }
 
-template <typename T, bool WIDE, bool ROOTED>
-__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) ll_reduce_kernel(const __grid_constant__ KArgs k) {
-  constexpr int KIND = ROOTED ? LL_REDUCE : LL_ALL_REDUCE;
-  switch (k.redop) {
-    case PDCC_SUM: run_ll<KIND, T, PDCC_SUM, WIDE>(k); break;
-    case PDCC_PRODUCT: run_ll<KIND, T, PDCC_PRODUCT, WIDE>(k); break;
-    case PDCC_MIN: run_ll<KIND, T, PDCC_MIN, WIDE>(k); break;
-    default: run_ll<KIND, T, PDCC_MAX, WIDE>(k); break;
-  }
+template <typename T, bool WIDE, int OP, bool ROOTED>
+__global__ void __launch_bounds__(kThreads, 1) ll_reduce_kernel(const __grid_constant__ KArgs k) {
+  run_ll<ROOTED ? LL_REDUCE : LL_ALL_REDUCE, T, OP, WIDE>(k);
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kThreads, kMinCtasPerSm) ll_move_kernel(const __grid_constant__ KArgs k) {
+__global__ void __launch_bounds__(kThreads, 1) ll_move_kernel(const __grid_constant__ KArgs k) {
   run_ll<KIND, uint8_t, PDCC_SUM, false>(k);
 }
 

@@ -19,13 +19,21 @@
 //     a stand-in, not a device address), and zeroes the flag and counter regions. That
 //     first call synchronises, so make it before any stream capture begins.
 //   * All calls on a device share the one array. Its ring counters and flags deliberately
-//     survive from call to call (they only ever grow, that is how slots are recycled);
-//     the per-call device-side error record is the one thing cleared on every call.
+//     survive from call to call (they only ever grow, that is how slots are recycled), and
+//     so does the device-side error record: a wait that timed out inside a kernel stays
+//     recorded until pdcc_emu2_noalloc_check() reads and clears it.
 //   * Because the array is shared, two calls that overlap on the GPU (different streams,
-//     or a graph replay racing a direct call) corrupt each other. Issue them on one stream.
-//   * Messages above PDCC_NOALLOC_MAX_BYTES are refused.
+//     or a replayed launch racing a direct call) corrupt each other. Issue them on one
+//     stream.
+//   * Messages above PDCC_NOALLOC_MAX_BYTES are refused; so are dtypes without a reduction
+//     kernel and tensors that do not live on `device` — all before anything is enqueued.
+//   * The per-rank kernel arguments reach the device as kernel parameters of a small
+//     set-up kernel, never through a copy from host memory, so nothing enqueued here keeps
+//     pointing at the caller's (or this function's) stack.
+//   * The caller's current device is left as it was found.
 // Nothing here calls cudaMalloc, cudaFree or any routine that allocates.
 #include <cuda_runtime.h>
+#include <string.h>
 
 #include <mutex>
 
@@ -37,7 +45,7 @@ namespace {
 
 constexpr int kRanks = 2;
 constexpr int kRings = 4;                         // CTAs per emulated rank
-constexpr size_t kSlotBytes = 256 * 1024;         // tile slot
+constexpr size_t kSlotBytes = 256 * 1024;         // a ring is PDCC_RING_DEPTH x this
 constexpr size_t kBlockBytes = kDataOffset + size_t(kRings) * PDCC_RING_DEPTH * kSlotBytes;
 constexpr size_t kArgsBytes = 4096;               // the per-rank kernel arguments
 constexpr size_t kNoallocScratchBytes = kRanks * kBlockBytes + kArgsBytes;
@@ -48,6 +56,25 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoallocScratch
 constexpr int kMaxDevices = 64;
 unsigned char* g_scratch_ptr[kMaxDevices] = {};  // device address of the array, per device
 std::mutex g_setup_mu;
+
+// Restores the caller's current device on every exit path.
+struct DeviceGuard {
+  int prev = -1;
+  bool armed = false;
+  int enter(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+      set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+      return PDCC_ECUDA;
+    }
+    armed = prev >= 0 && prev != device;
+    return PDCC_OK;
+  }
+  ~DeviceGuard() {
+    if (armed) cudaSetDevice(prev);
+  }
+};
 
 // Once per device, with that device current: resolve the array's device address and put
 // the regions that must start at zero (error record, ring counters, flags, LL packets)
@@ -82,6 +109,24 @@ int setup_device(int device, unsigned char** out) {
   return PDCC_OK;
 }
 
+// The tensor must be device memory of `device` (or managed memory, which every device
+// reaches): a host pointer or another GPU's memory would fault inside the kernel.
+int check_on_device(const void* p, int device, const char* what) {
+  cudaPointerAttributes at;
+  cudaError_t e = cudaPointerGetAttributes(&at, p);
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_error("no-alloc all_reduce: cannot query %s: %s", what, cudaGetErrorString(e));
+    return PDCC_EINVAL;
+  }
+  if (at.type == cudaMemoryTypeManaged) return PDCC_OK;
+  if (at.type != cudaMemoryTypeDevice || at.device != device) {
+    set_error("no-alloc all_reduce: %s is not device memory of device %d", what, device);
+    return PDCC_EINVAL;
+  }
+  return PDCC_OK;
+}
+
 }  // namespace
 
 extern "C" int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, uint64_t count,
@@ -95,9 +140,9 @@ extern "C" int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, 
     return PDCC_EINVAL;
   }
   const size_t esz = dtype_size(dtype);
-  if (esz == 0) {
-    set_error("no-alloc all_reduce: unsupported dtype %d", dtype);
-    return PDCC_EINVAL;
+  if (esz == 0 || !reduce_supported(dtype, redop)) {
+    set_error("no-alloc all_reduce: no reduction kernel for dtype %d with op %d", dtype, redop);
+    return PDCC_EUNSUPPORTED;
   }
   if (count == 0) return PDCC_OK;
   if (count > PDCC_NOALLOC_MAX_BYTES / esz) {
@@ -107,13 +152,13 @@ extern "C" int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, 
               static_cast<unsigned long long>(PDCC_NOALLOC_MAX_BYTES));
     return PDCC_EINVAL;
   }
-  cudaError_t e = cudaSetDevice(device);  // the address below is only valid for this device
-  if (e != cudaSuccess) {
-    set_error("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
-    return PDCC_ECUDA;
-  }
+  DeviceGuard guard;  // the address below is only valid with `device` current
+  int rc = guard.enter(device);
+  if (rc != PDCC_OK) return rc;
+  if ((rc = check_on_device(buf0, device, "buf0")) != PDCC_OK) return rc;
+  if ((rc = check_on_device(buf1, device, "buf1")) != PDCC_OK) return rc;
   unsigned char* scratch = nullptr;
-  int rc = setup_device(device, &scratch);
+  rc = setup_device(device, &scratch);
   if (rc != PDCC_OK) return rc;
 
   pdcc_op_t op;
@@ -135,7 +180,7 @@ extern "C" int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, 
     for (int p = 0; p < kRanks; ++p)
       d.base[p] = reinterpret_cast<char*>(scratch) + size_t(p) * kBlockBytes;
     d.mc = nullptr;
-    d.slot_bytes = uint32_t(kSlotBytes);
+    d.ring_bytes = uint32_t(kSlotBytes * PDCC_RING_DEPTH);
     d.timeout_ms = 5000;
     host[r].in = bufs[r];
     host[r].out = bufs[r];
@@ -144,20 +189,50 @@ extern "C" int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, 
   rc = plan_collective(host[0].comm, kRings, false, op, &plan);
   if (rc != PDCC_OK) return rc;
 
-  cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // the one thing a call must find at zero: the device-side error record of each block
-  for (int r = 0; r < kRanks; ++r) {
-    e = cudaMemsetAsync(scratch + size_t(r) * kBlockBytes, 0, 2 * sizeof(uint32_t), st);
-    if (e != cudaSuccess) {
-      set_error("clearing the no-alloc error record: %s", cudaGetErrorString(e));
-      return PDCC_ECUDA;
-    }
-  }
   RankArgs* dev_args = reinterpret_cast<RankArgs*>(scratch + size_t(kRanks) * kBlockBytes);
-  e = cudaMemcpyAsync(dev_args, host, sizeof(RankArgs) * kRanks, cudaMemcpyHostToDevice, st);
+  rc = upload_rank_args(host, kRanks, dev_args, stream);  // kernel parameters, not a memcpy
+  if (rc != PDCC_OK) return rc;
+  return launch_collective(host, kRanks, dev_args, op, plan, stream);
+}
+
+// Waits for the device and reports (then clears) a device-side wait that ran out of time in
+// any no-alloc call since the last check. Allocates nothing either.
+extern "C" int pdcc_emu2_noalloc_check(int device) {
+  if (device < 0 || device >= kMaxDevices) {
+    set_error("no-alloc check: device %d out of range", device);
+    return PDCC_EINVAL;
+  }
+  DeviceGuard guard;
+  int rc = guard.enter(device);
+  if (rc != PDCC_OK) return rc;
+  unsigned char* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> g(g_setup_mu);
+    scratch = g_scratch_ptr[device];
+  }
+  cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
-    set_error("uploading the no-alloc kernel arguments: %s", cudaGetErrorString(e));
+    set_error("no-alloc check on device %d: %s", device, cudaGetErrorString(e));
     return PDCC_ECUDA;
   }
-  return launch_collective(host, kRanks, dev_args, op, plan, stream);
+  if (scratch == nullptr) return PDCC_OK;  // never used on this device
+  for (int r = 0; r < kRanks; ++r) {
+    uint32_t err[2] = {0, 0};
+    unsigned char* rec = scratch + size_t(r) * kBlockBytes;
+    e = cudaMemcpy(err, rec, sizeof(err), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) {
+      set_error("no-alloc check: reading the error record: %s", cudaGetErrorString(e));
+      return PDCC_ECUDA;
+    }
+    if (err[0] != 0) {
+      const uint32_t info = err[1];
+      uint32_t zero[2] = {0, 0};
+      cudaMemcpy(rec, zero, sizeof(zero), cudaMemcpyHostToDevice);
+      set_error("no-alloc all_reduce: a device-side wait timed out on emulated rank %d "
+                "(channel %u, waiting on rank %u, flag value 0x%06x); the output of that call is "
+                "not valid", r, info >> 28, (info >> 24) & 0xfu, info & 0xffffffu);
+      return PDCC_EPEER;
+    }
+  }
+  return PDCC_OK;
 }

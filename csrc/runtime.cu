@@ -264,7 +264,8 @@ struct pdcc_comm {
   int kind = PDCC_HANDLE_LOCAL;
   int sm_count = 0;
   int max_blocks = PDCC_MAX_BLOCKS;
-  size_t slot_bytes = 0;
+  size_t slot_bytes = 0;   // configured quarter-ring (ring_bytes = PDCC_RING_DEPTH x this)
+  size_t ring_bytes = 0;
   size_t block_bytes = 0;
   size_t heap_off = 0;
   bool has_mc = false;
@@ -391,7 +392,7 @@ int pdcc_probe(int device, pdcc_caps_t* caps) {
 static int fill_dev(pdcc_comm* c) {
   c->dev.rank = c->cfg.rank;
   c->dev.nranks = c->cfg.nranks;
-  c->dev.slot_bytes = uint32_t(c->slot_bytes);
+  c->dev.ring_bytes = uint32_t(c->ring_bytes);
   c->dev.timeout_ms = uint32_t(c->cfg.device_timeout_ms > 0 ? c->cfg.device_timeout_ms : 10000);
   for (int p = 0; p < PDCC_MAX_RANKS; ++p) c->dev.base[p] = nullptr;
   for (int p = 0; p < c->cfg.nranks; ++p) {
@@ -403,10 +404,14 @@ static int fill_dev(pdcc_comm* c) {
 }
 
 static void sizes_from_cfg(pdcc_comm* c) {
-  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(2) << 20);
+  // One CTA's ring is PDCC_RING_DEPTH x slot_bytes; every call cuts it into slots of its own
+  // size (plan_collective). 1 MiB per ring by default: 148 rings + header = 166 MiB per
+  // communicator, and the tiles in flight on a GPU (~75 MB) stay inside the 126 MB L2.
+  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(256) << 10);
+  c->ring_bytes = c->slot_bytes * PDCC_RING_DEPTH;
   c->max_blocks = c->cfg.max_blocks > 0 ? c->cfg.max_blocks : PDCC_MAX_BLOCKS;
   if (c->max_blocks > PDCC_MAX_BLOCKS) c->max_blocks = PDCC_MAX_BLOCKS;
-  c->heap_off = kDataOffset + size_t(c->max_blocks) * PDCC_RING_DEPTH * c->slot_bytes;
+  c->heap_off = round_up_sz(kDataOffset + size_t(c->max_blocks) * c->ring_bytes, size_t(2) << 20);
   c->block_bytes = c->heap_off + c->cfg.heap_bytes;
 }
 
@@ -779,7 +784,7 @@ static int ring_limit(const pdcc_comm* c) {
 }
 
 int pdcc_plan(pdcc_comm_t* c, const pdcc_op_t* op, int* algo, int* nblocks, int* threads,
-              uint64_t* tile_bytes, int* ntiles) {
+              uint64_t* tile_bytes, int* ntiles, int* depth, uint32_t* slot_stride) {
   if (!c || !op) return PDCC_EINVAL;
   Plan p;
   int rc = plan_collective(c->dev, ring_limit(c), c->has_mc, *op, &p);
@@ -789,17 +794,20 @@ int pdcc_plan(pdcc_comm_t* c, const pdcc_op_t* op, int* algo, int* nblocks, int*
   if (threads) *threads = p.threads;
   if (tile_bytes) *tile_bytes = p.tile_bytes;
   if (ntiles) *ntiles = p.ntiles;
+  if (depth) *depth = p.depth;
+  if (slot_stride) *slot_stride = p.slot_stride;
   return PDCC_OK;
 }
 
 int pdcc_plan_dry(int nranks, int has_multicast, size_t slot_bytes, int rings, const pdcc_op_t* op,
-                  int* algo, int* nblocks, int* threads, uint64_t* tile_bytes, int* ntiles) {
+                  int* algo, int* nblocks, int* threads, uint64_t* tile_bytes, int* ntiles,
+                  int* depth, uint32_t* slot_stride) {
   if (!op || nranks < 1 || nranks > PDCC_MAX_RANKS) return PDCC_EINVAL;
   DevComm dev;
   memset(&dev, 0, sizeof(dev));
   dev.rank = 0;
   dev.nranks = nranks;
-  dev.slot_bytes = uint32_t(slot_bytes ? slot_bytes : (size_t(2) << 20));
+  dev.ring_bytes = uint32_t((slot_bytes ? slot_bytes : (size_t(256) << 10)) * PDCC_RING_DEPTH);
   dev.mc = has_multicast ? reinterpret_cast<char*>(uintptr_t(16)) : nullptr;  // never dereferenced
   Plan p;
   int rc = plan_collective(dev, rings > 0 ? rings : PDCC_MAX_BLOCKS, has_multicast != 0, *op, &p);
@@ -809,6 +817,8 @@ int pdcc_plan_dry(int nranks, int has_multicast, size_t slot_bytes, int rings, c
   if (threads) *threads = p.threads;
   if (tile_bytes) *tile_bytes = p.tile_bytes;
   if (ntiles) *ntiles = p.ntiles;
+  if (depth) *depth = p.depth;
+  if (slot_stride) *slot_stride = p.slot_stride;
   return PDCC_OK;
 }
 
@@ -1012,7 +1022,7 @@ int pdcc_emu_create(int device, int nranks, size_t slot_bytes, int max_blocks,
   if (e->max_blocks > PDCC_MAX_BLOCKS) e->max_blocks = PDCC_MAX_BLOCKS;
   // every emulated rank's CTAs must be resident at once
   if (e->max_blocks * nranks > caps.sm_count) e->max_blocks = caps.sm_count / nranks;
-  e->block_bytes = kDataOffset + size_t(e->max_blocks) * PDCC_RING_DEPTH * e->slot_bytes;
+  e->block_bytes = kDataOffset + size_t(e->max_blocks) * PDCC_RING_DEPTH * e->slot_bytes;  // rings of DEPTH x slot
   for (int r = 0; r < nranks; ++r) {
     cudaError_t ce = cudaMalloc(reinterpret_cast<void**>(&e->blocks[r]), e->block_bytes);
     if (ce == cudaSuccess) ce = cudaMemset(e->blocks[r], 0, kZeroBytes);
@@ -1035,7 +1045,7 @@ int pdcc_emu_create(int device, int nranks, size_t slot_bytes, int max_blocks,
     d.nranks = nranks;
     for (int p = 0; p < nranks; ++p) d.base[p] = e->blocks[p];
     d.mc = nullptr;
-    d.slot_bytes = uint32_t(e->slot_bytes);
+    d.ring_bytes = uint32_t(e->slot_bytes * PDCC_RING_DEPTH);
     d.timeout_ms = uint32_t(device_timeout_ms > 0 ? device_timeout_ms : 5000);
   }
   cudaDeviceSynchronize();
@@ -1067,9 +1077,9 @@ int pdcc_emu_collective(pdcc_emu_t* e, const pdcc_op_t* ops, void* stream) {
   int rc = plan_collective(e->dev[0], limit, false, op0, &p);
   if (rc) return rc;
   if (e->nranks == 1) return launch_collective(host, 1, nullptr, op0, p, stream);
-  // pageable source: the copy is staged before this returns, so `host` may die
-  CUDA_TRY(cudaMemcpyAsync(e->dev_args, host, sizeof(RankArgs) * e->nranks,
-                           cudaMemcpyHostToDevice, static_cast<cudaStream_t>(stream)));
+  // by value through a set-up kernel: the stream never reads `host` (common.h)
+  rc = upload_rank_args(host, e->nranks, e->dev_args, stream);
+  if (rc) return rc;
   return launch_collective(host, e->nranks, e->dev_args, op0, p, stream);
 }
 

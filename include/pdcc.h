@@ -32,7 +32,7 @@ extern "C" {
 
 #define PDCC_MAX_RANKS 8      /* one NVSwitch domain of an HGX B200 board      */
 #define PDCC_MAX_BLOCKS 148   /* CTAs (= private tile rings) per collective: one per SM */
-#define PDCC_RING_DEPTH 4     /* tile slots per CTA ring                       */
+#define PDCC_RING_DEPTH 4     /* LL slots per CTA ring; a data ring is DEPTH x slot_bytes */
 
 /* error codes */
 #define PDCC_OK 0
@@ -113,7 +113,9 @@ typedef struct {
   int multicast;          /* -1 auto, 0 never, 1 require                      */
   int timeout_ms;         /* host-side rendezvous timeout                     */
   int device_timeout_ms;  /* device-side flag wait timeout (0 = default 10 s) */
-  size_t slot_bytes;      /* per-CTA tile slot capacity (0 = default 2 MiB)   */
+  size_t slot_bytes;      /* a CTA's ring is PDCC_RING_DEPTH x this; every call
+                             cuts the ring into slots for its own tile size
+                             (0 = default 256 KiB, i.e. 1 MiB rings)          */
   int max_blocks;         /* rings to provision (0 = PDCC_MAX_BLOCKS)         */
   size_t heap_bytes;      /* symmetric heap for zero-copy tensors (0 = none)  */
   char key[64];           /* unique per group: namespaces the store keys      */
@@ -214,13 +216,18 @@ int pdcc_barrier(pdcc_comm_t* comm, void* stream);
 
 /* What `algo`/`nblocks` AUTO resolves to for this op on this comm. */
 int pdcc_plan(pdcc_comm_t* comm, const pdcc_op_t* op, int* algo, int* nblocks, int* threads,
-              uint64_t* tile_bytes, int* ntiles);
+              uint64_t* tile_bytes, int* ntiles, int* depth, uint32_t* slot_stride);
 
 /* The same planner without a communicator (and without a GPU): what AUTO would resolve to
  * for `op` on a group of `nranks` with `slot_bytes` slots and `rings` usable CTAs, with or
  * without a multicast mapping. Used by the CPU tests of the size -> variant table. */
 int pdcc_plan_dry(int nranks, int has_multicast, size_t slot_bytes, int rings, const pdcc_op_t* op,
-                  int* algo, int* nblocks, int* threads, uint64_t* tile_bytes, int* ntiles);
+                  int* algo, int* nblocks, int* threads, uint64_t* tile_bytes, int* ntiles,
+                  int* depth, uint32_t* slot_stride);
+
+/* The planner reads its PDCC_* knobs from the environment once and caches them (it runs on
+ * every call). Call this after changing one in a live process (benchmarks do). */
+void pdcc_reload_env(void);
 
 /* Number of kernels this library has launched in this process (bench.py's
  * gpu_launches claim is read from here, not estimated). */

@@ -109,6 +109,8 @@ def lib() -> C.CDLL:
     L.pdcc_last_error.restype = cp
     L.pdcc_version.restype = cp
     L.pdcc_launch_count.restype = C.c_uint64
+    L.pdcc_reload_env.restype = None
+    L.pdcc_reload_env.argtypes = []
     sigs = {
         "pdcc_store_server_start": [cp, ci, C.POINTER(vp), C.POINTER(ci)],
         "pdcc_store_server_stop": [vp],
@@ -127,9 +129,10 @@ def lib() -> C.CDLL:
         "pdcc_comm_check": [vp],
         "pdcc_collective": [vp, C.POINTER(Op), vp],
         "pdcc_plan": [vp, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci),
-                      C.POINTER(C.c_uint64), C.POINTER(ci)],
+                      C.POINTER(C.c_uint64), C.POINTER(ci), C.POINTER(ci), C.POINTER(C.c_uint32)],
         "pdcc_plan_dry": [ci, ci, C.c_size_t, ci, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci),
-                          C.POINTER(ci), C.POINTER(C.c_uint64), C.POINTER(ci)],
+                          C.POINTER(ci), C.POINTER(C.c_uint64), C.POINTER(ci), C.POINTER(ci),
+                          C.POINTER(C.c_uint32)],
         "pdcc_emu_create": [ci, ci, C.c_size_t, ci, ci, C.POINTER(vp)],
         "pdcc_emu_destroy": [vp],
         "pdcc_emu_collective": [vp, C.POINTER(Op), vp],
@@ -166,13 +169,20 @@ def plan_dry(nranks: int, coll: int, count: int, dtype: int, *, has_multicast: b
     op = Op()
     op.coll, op.dtype, op.out_dtype, op.redop = coll, dtype, dtype, redop
     op.algo, op.nblocks, op.scale, op.count = algo, nblocks, 1.0, count
-    a, b, t, n = C.c_int(), C.c_int(), C.c_int(), C.c_int()
-    tb = C.c_uint64()
+    a, b, t, n, d = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    tb, ss = C.c_uint64(), C.c_uint32()
     check(lib().pdcc_plan_dry(nranks, int(has_multicast), slot_bytes, rings, C.byref(op),
-                              C.byref(a), C.byref(b), C.byref(t), C.byref(tb), C.byref(n)))
+                              C.byref(a), C.byref(b), C.byref(t), C.byref(tb), C.byref(n),
+                              C.byref(d), C.byref(ss)))
     names = {v: k for k, v in ALGO_NAMES.items()}
     return {"algo": names.get(a.value, a.value), "nblocks": b.value, "threads": t.value,
-            "tile_bytes": tb.value, "ntiles": n.value}
+            "tile_bytes": tb.value, "ntiles": n.value, "depth": d.value,
+            "slot_stride": ss.value}
+
+
+def reload_env() -> None:
+    """Make the native planner re-read its PDCC_* knobs (it caches them at first use)."""
+    lib().pdcc_reload_env()
 
 
 def launch_count() -> int:

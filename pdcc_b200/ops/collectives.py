@@ -130,13 +130,14 @@ class NativeComm:
              nblocks: int = 0) -> dict:
         """What AUTO resolves to for this op (algo, CTAs, tile size): bench/debug only."""
         op = _fill(N.Op(), coll, count, dtype_code(dtype), redop=redop, algo=algo, nblocks=nblocks)
-        a, b, t, n = C.c_int(), C.c_int(), C.c_int(), C.c_int()
-        tb = C.c_uint64()
+        a, b, t, n, d = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        tb, ss = C.c_uint64(), C.c_uint32()
         N.check(N.lib().pdcc_plan(self._h, C.byref(op), C.byref(a), C.byref(b), C.byref(t),
-                                  C.byref(tb), C.byref(n)))
+                                  C.byref(tb), C.byref(n), C.byref(d), C.byref(ss)))
         names = {v: k for k, v in N.ALGO_NAMES.items()}
         return {"algo": names.get(a.value, a.value), "nblocks": b.value, "threads": t.value,
-                "tile_bytes": tb.value, "ntiles": n.value}
+                "tile_bytes": tb.value, "ntiles": n.value, "depth": d.value,
+                "slot_stride": ss.value}
 
     def check(self) -> None:
         """Synchronises and raises if a device-side wait timed out in any kernel so far."""
