@@ -101,6 +101,51 @@ class Suite:
         self.c_all_gather()
         self.c_broadcast()
 
+    # ---- correctness of the very buffers that were timed -------------------------------
+    def verify(self) -> dict:
+        """Each of the six collectives once more, on rank- and position-dependent inputs
+        (x_r[i] = i % 251 + r + 1, exact in fp32), checked element by element against the
+        closed form on every rank. Returns {collective: bool} for this rank."""
+        import torch
+
+        n, r, dev = self.size, self.rank, self.dev
+        pat = lambda m: (torch.arange(m, device=dev) % 251).to(torch.float32)  # noqa: E731
+        pc, ps = pat(self.count), pat(self.shard)
+        tri = n * (n + 1) / 2.0
+        ok = {}
+        self.t_red.copy_(pc + (r + 1))
+        self.c_reduce()
+        ok["reduce"] = bool(torch.equal(self.t_red, n * pc + tri if r == 0 else pc + (r + 1)))
+        self.t_ar.copy_(pc + (r + 1))
+        self.c_all_reduce()
+        ok["all_reduce"] = bool(torch.equal(self.t_ar, n * pc + tri))
+        if r == 0:
+            for j, t in enumerate(self.sc_list):
+                t.copy_(ps + 1000.0 * (j + 1))
+        self.sc_out.zero_()
+        self.c_scatter()
+        ok["scatter"] = bool(torch.equal(self.sc_out, ps + 1000.0 * (r + 1)))
+        self.ga_in.copy_(ps + 1000.0 * (r + 1))
+        for t in self.ga_list:
+            t.zero_()
+        self.c_gather()
+        ok["gather"] = all(bool(torch.equal(t, ps + 1000.0 * (j + 1)))
+                           for j, t in enumerate(self.ga_list))
+        self.ag_in.copy_(ps + 1000.0 * (r + 1))
+        for t in self.ag_list:
+            t.zero_()
+        self.c_all_gather()
+        ok["all_gather"] = all(bool(torch.equal(t, ps + 1000.0 * (j + 1)))
+                               for j, t in enumerate(self.ag_list))
+        if r == 0:
+            self.t_bc.copy_(pc + 7.0)
+        else:
+            self.t_bc.zero_()
+        self.c_broadcast()
+        ok["broadcast"] = bool(torch.equal(self.t_bc, pc + 7.0))
+        torch.cuda.synchronize()
+        return ok
+
     # ---- end to end: inputs come from pinned host memory, results go back ------------
     def make_host(self):
         import torch
@@ -207,6 +252,18 @@ def run(D, rank: int, size: int, args, launch_count) -> dict:
         lat.append(timed(lambda: D.all_reduce(small, op=D.ReduceOp.SUM, group=suite.group), 200))
     small_p50 = statistics.median(lat) * 1e3
 
+    # ---- verification: the timed call sites, on checkable inputs, on every rank ----------
+    mine = suite.verify()
+    bad = [k for k, v in mine.items() if not v]
+    flag = torch.tensor([0.0 if bad else 1.0], dtype=torch.float64)
+    if tdist.get_backend() == "nccl":
+        flag = flag.to(dev)
+    tdist.all_reduce(flag, op=tdist.ReduceOp.MIN)
+    verified = bool(flag.item() == 1.0)
+    if bad:
+        print(f"[rank {rank}] verification FAILED for: {bad}", file=sys.stderr, flush=True)
+    sync_all()
+
     # ---- end to end ------------------------------------------------------------------
     e2e = None
     if not args.no_e2e:
@@ -246,7 +303,7 @@ def run(D, rank: int, size: int, args, launch_count) -> dict:
                                 "(nccl-tests factors) is in per_collective",
         },
         "per_collective": per, "small_msg_p50_us": round(small_p50, 2),
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "verified": verified,
     }
 
 
@@ -286,6 +343,8 @@ def main() -> None:
         if rank == 0:
             print(json.dumps(result), flush=True)
         D.destroy_process_group()
+        if not result["verified"]:
+            raise SystemExit(3)
         return
 
     # ---- reference arm: the UNMODIFIED reference's own init_process, on NCCL ------------
@@ -312,6 +371,8 @@ def main() -> None:
         out["result"]["gpu_launches"] = None
         print(json.dumps(out["result"]), flush=True)
     tdist.destroy_process_group()
+    if not out["result"]["verified"]:
+        raise SystemExit(3)
 
 
 if __name__ == "__main__":

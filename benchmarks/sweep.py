@@ -21,6 +21,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 NVLINK_GBPS = 770.0
+COLL_ID = {"all_reduce": 0, "reduce": 1, "broadcast": 2, "scatter": 3, "gather": 4, "all_gather": 5}
 
 
 def parse_size(s: str) -> int:
@@ -77,6 +78,7 @@ def main() -> None:
     import torch.distributed as tdist
 
     import pdcc_b200 as dist
+    from pdcc_b200 import _native as N
     from pdcc_b200.ops import collectives as K
 
     rank = int(os.environ.get("RANK", "0"))
@@ -214,13 +216,26 @@ def main() -> None:
                             for ev in (env_values if impl == "pdcc" else [None])]
                 for algo, nb, ev in variants:
                     if env_name is not None and ev is not None:
-                        os.environ[env_name] = ev  # same value on every rank: same plan
+                        # same value on every rank: same plan. Several knobs at once are
+                        # written NAME=a+OTHER=b inside one value.
+                        for kv in (f"{env_name}={ev}").split("+"):
+                            kk, vv = kv.split("=", 1)
+                            os.environ[kk] = vv
+                        N.reload_env()
                     if algo == "ll" and real > (1 << 20):
                         continue  # LL doubles the wire bytes: a small-message variant only
                     if not member or (impl == "pdcc" and comm is None):
                         # non-members still take part in the host-side timing collectives
                         us = timed(lambda: None, real)
                         continue
+                    if impl == "pdcc":
+                        try:  # a variant this collective / group cannot run: same answer on every rank
+                            comm.plan(COLL_ID[coll], count if coll in ("all_reduce", "reduce") else
+                                      real if coll == "broadcast" else shard * esz,
+                                      torch.uint8 if coll not in ("all_reduce", "reduce") else dtype,
+                                      redop=kop, algo=None if algo == "auto" else algo, nblocks=nb)
+                        except N.PdccError:
+                            continue
                     us = timed(make(impl, algo, nb), real)
                     graph_us = None
                     if args.graph and real <= args.graph_max:
@@ -238,8 +253,7 @@ def main() -> None:
                     if env_name is not None and impl == "pdcc":
                         row["env"] = {env_name: ev}
                     if impl == "pdcc":
-                        row["plan"] = comm.plan({"all_reduce": 0, "reduce": 1, "broadcast": 2,
-                                                 "scatter": 3, "gather": 4, "all_gather": 5}[coll],
+                        row["plan"] = comm.plan(COLL_ID[coll],
                                                 count if coll in ("all_reduce", "reduce") else
                                                 real if coll == "broadcast" else shard * esz,
                                                 torch.uint8 if coll not in ("all_reduce", "reduce") else dtype,

@@ -36,7 +36,9 @@ constexpr size_t kFlagWords = size_t(kNumChannels) * PDCC_MAX_BLOCKS * PDCC_MAX_
 // the flag channels inside the pad region, so that every rank can add to every rank's copy
 // through the multicast alias. Word kSymArriveWord + 2*b + phase of the pad region.
 constexpr size_t kSymArriveWord = kFlagWords;
-constexpr size_t kPadBytes = (kFlagWords + 2 * PDCC_MAX_BLOCKS) * sizeof(uint32_t);
+// Progress counters of the two-phase zero-copy broadcast: word kSymProgWord + 2*b + half.
+constexpr size_t kSymProgWord = kSymArriveWord + 2 * PDCC_MAX_BLOCKS;
+constexpr size_t kPadBytes = (kFlagWords + 4 * PDCC_MAX_BLOCKS) * sizeof(uint32_t);
 constexpr size_t kHeaderBytes = 2 * 1024 * 1024;  // keeps rings 2 MiB aligned
 static_assert(kCtrlBytes + kPadBytes <= kHeaderBytes, "header too small");
 // LL (low-latency) slots hold {data, flag, data, flag} packets only, never raw payload, so
@@ -53,6 +55,14 @@ constexpr int kCtrlErr = 0;        // first device-side timeout record: code
 constexpr int kCtrlErrInfo = 1;    // .. chan | tile | peer packed
 constexpr int kCtrlEpoch = 64;     // + b : tiles processed so far by CTA index b
 constexpr int kCtrlSymEpoch = 256;  // + b : zero-copy (symmetric heap) calls made by CTA index b
+// Optional timeline of CTA 0 (PDCC_TRACE=1): word kCtrlTrace counts the events, 8-word
+// records {kind, tile, begin_lo, begin_hi, end_lo, end_hi, aux0, aux1} follow at +4.
+// kind: 0..2 worker of that stage (| warp << 8): begin = started waiting for admission,
+// end = tile finished, aux0 = ns spent waiting; 16 publisher: the fence, aux0 = tiles done
+// per stage (10 bits each); 32..34 admitter: the moment tile `tile` of that stage was admitted.
+constexpr int kCtrlTrace = 4096;
+constexpr int kCtrlTraceCap = (int(kCtrlBytes / 4) - kCtrlTrace - 4) / 8;
+constexpr int kCtrlSymProg = 512;   // + 2*b + half : tiles the two-phase zero-copy broadcast dealt so far
 
 // What a kernel needs to know about the group, passed by value (88 bytes).
 struct DevComm {
@@ -98,5 +108,17 @@ size_t dtype_size(int dtype);
 int upload_rank_args(const RankArgs* host, int n, RankArgs* dev, void* stream);
 // True when (dtype, redop) has an all_reduce kernel (P2P variants).
 bool reduce_supported(int dtype, int redop);
+
+// Zero-copy collectives on symmetric memory (sym.cuh). `in`/`out` are described by their
+// local address plus the multicast alias / peer addresses of the same offset.
+struct SymTensor {
+  char* local = nullptr;
+  char* mc = nullptr;
+  char* peer[PDCC_MAX_RANKS] = {};
+};
+bool sym_supported(int coll, int dtype, int redop);
+uint64_t sym_min_bytes(int nranks);  // at or below this size AUTO keeps the staged small-message kernels
+int launch_sym(const DevComm& comm, int ring_limit, const pdcc_op_t& op, const SymTensor& in,
+               const SymTensor& out, void* stream);
 
 }  // namespace pdcc

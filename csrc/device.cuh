@@ -226,28 +226,36 @@ __device__ __forceinline__ void spin_until(const Ctx& c, int chan, int src, uint
   }
 }
 
-// ---- group-scoped acquire / release, the only synchronisation of the tile pipeline -----
-//
-// group_wait: thread i (< nranks) of the group polls rank i's flag, then issues a
-// system-scope fence (flag load + fence = acquire); the group barrier hands the guarantee
-// to every thread of the group. group_post: the group barrier orders every thread's writes
-// before thread i's fence (cumulativity), the fence publishes them at system scope, then
-// the relaxed flag store to rank i's pad completes the release. Both follow the PTX memory
-// model to the letter; nothing relies on control dependencies or on store ordering that the
-// model does not promise.
-__device__ __forceinline__ void group_wait(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
-  if (c.tid < c.n && ((mask >> c.tid) & 1u)) {
-    if (!*reinterpret_cast<volatile int*>(c.poisoned)) spin_until(c, chan, c.tid, val);
-    fence_acq_rel_sys();
-  }
-  group_sync(c);
+// ---- CTA-scope hand-offs between the worker warps and the two control warps --------------
+__device__ __forceinline__ uint32_t ld_acquire_cta_shared(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.cta.shared.u32 %0, [%1];"
+               : "=r"(v)
+               : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(p)))
+               : "memory");
+  return v;
 }
-__device__ __forceinline__ void group_post(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
-  group_sync(c);
-  if (c.tid < c.n && ((mask >> c.tid) & 1u)) {
-    fence_acq_rel_sys();
-    uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[c.tid] + kCtrlBytes);
-    st_relaxed_sys(pad + flag_index(chan, c.b, c.rank), val);
+__device__ __forceinline__ void st_release_cta_shared(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(p))),
+               "r"(v)
+               : "memory");
+}
+__device__ __forceinline__ void red_release_cta_shared_add(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.cta.shared.add.u32 [%0], %1;" ::"r"(
+                   static_cast<uint32_t>(__cvta_generic_to_shared(p))),
+               "r"(v)
+               : "memory");
+}
+
+// Raises flag[chan][b][my rank] = val on every rank in mask (relaxed stores; the caller has
+// issued the fence that makes them the tail of a release pattern).
+__device__ __forceinline__ void post_flags(const Ctx& c, int chan, uint32_t val, uint32_t mask) {
+  for (int p = 0; p < c.n; ++p) {
+    if ((mask >> p) & 1u) {
+      uint32_t* pad = reinterpret_cast<uint32_t*>(c.a->comm.base[p] + kCtrlBytes);
+      st_relaxed_sys(pad + flag_index(chan, c.b, c.rank), val);
+    }
   }
 }
 
@@ -300,20 +308,26 @@ __device__ __forceinline__ bool aligned16(const void* p) {
 // only its few arguments live, instead of competing with everything the (heavily inlined,
 // four-ops-in-one) kernel body keeps alive. The call costs nothing next to a tile.
 
-// 16-byte vector copy of n16 units, UNROLL independent loads in flight per thread.
+// 16-byte vector copy of n16 units, UNROLL independent loads in flight per thread. Every
+// pass issues all of its (predicated) loads before its first store, the last partial pass
+// included: a range shorter than one pass still has n16 / nt loads in flight per thread
+// instead of degrading to one load -> one store round trips.
 template <int UNROLL>
 __device__ __noinline__ void copy16(char* __restrict__ d, const char* __restrict__ s, size_t n16,
                                     int tid, int nt) {
-  const size_t pass = size_t(nt) * UNROLL;
-  const size_t nmain = n16 / pass * pass;
-  for (size_t i = tid; i < nmain; i += pass) {
+  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
     uint4 v[UNROLL];
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) v[k] = ld_stream_v4(s + ((i + size_t(k) * nt) << 4));
+    for (int k = 0; k < UNROLL; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      if (j < n16) v[k] = ld_stream_v4(s + (j << 4));
+    }
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) st_v4(d + ((i + size_t(k) * nt) << 4), v[k]);
+    for (int k = 0; k < UNROLL; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      if (j < n16) st_v4(d + (j << 4), v[k]);
+    }
   }
-  for (size_t i = nmain + tid; i < n16; i += nt) st_v4(d + (i << 4), ld_stream_v4(s + (i << 4)));
 }
 
 // CTA-wide copy of n bytes. Fast path: both sides 16-byte aligned. Anything else degrades
@@ -346,17 +360,7 @@ __device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nran
                                         int tid, int nt) {
   if (mask == 0) return;  // a group of one has nobody to push to
   if ((mask & (mask - 1u)) == 0) {  // one target: scatter, gather, reduce-scatter phase
-    char* d = base[__ffs(int(mask)) - 1] + off;
-    const size_t pass = size_t(nt) * UNROLL;
-    const size_t nmain = n16 / pass * pass;
-    for (size_t i = tid; i < nmain; i += pass) {
-      uint4 v[UNROLL];
-#pragma unroll
-      for (int k = 0; k < UNROLL; ++k) v[k] = ld_stream_v4(s + ((i + size_t(k) * nt) << 4));
-#pragma unroll
-      for (int k = 0; k < UNROLL; ++k) st_v4(d + ((i + size_t(k) * nt) << 4), v[k]);
-    }
-    for (size_t i = nmain + tid; i < n16; i += nt) st_v4(d + (i << 4), ld_stream_v4(s + (i << 4)));
+    copy16<UNROLL>(base[__ffs(int(mask)) - 1] + off, s, n16, tid, nt);
     return;
   }
   // several targets: every loaded unit is stored to each of them
@@ -366,7 +370,7 @@ __device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nran
 #pragma unroll
     for (int k = 0; k < U2; ++k) {
       const size_t j = i + size_t(k) * nt;
-      v[k] = ld_stream_v4(s + ((j < n16 ? j : i) << 4));
+      if (j < n16) v[k] = ld_stream_v4(s + (j << 4));
     }
 #pragma unroll
     for (int p = 0; p < PDCC_MAX_RANKS; ++p) {
@@ -377,6 +381,35 @@ __device__ __noinline__ void push16_p2p(char* const* __restrict__ base, int nran
           const size_t j = i + size_t(k) * nt;
           if (j < n16) st_v4(d + (j << 4), v[k]);
         }
+      }
+    }
+  }
+}
+
+// Dealing loop of the two-shot / two-phase collectives: the tile [src, src + n16 units) is
+// cut into parts of `sub16` units, part o belongs to rank owner[o] and goes to
+// base[owner[o]] + dst_off + (position inside the part). ONE streaming loop over the whole
+// tile (full passes of UNROLL loads in flight) instead of one short loop per owner; the
+// part owned by this rank itself (skip) is not sent.
+template <int UNROLL>
+__device__ __noinline__ void deal16(char* const* __restrict__ base, int first, int nranks,
+                                    int skip, size_t dst_off, size_t part_stride,
+                                    const char* __restrict__ s, size_t n16, size_t sub16, int tid,
+                                    int nt) {
+  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
+    uint4 v[UNROLL];
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      if (j < n16) v[k] = ld_stream_v4(s + (j << 4));
+    }
+#pragma unroll
+    for (int k = 0; k < UNROLL; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      if (j < n16) {
+        const uint32_t o = uint32_t(j) / uint32_t(sub16);  // a tile is far below 2^32 units
+        const int r = (first + int(o)) % nranks;
+        if (r != skip) st_v4(base[r] + dst_off + o * part_stride + ((j - o * sub16) << 4), v[k]);
       }
     }
   }
@@ -393,17 +426,19 @@ __device__ __forceinline__ void push_p2p(const Ctx& c, size_t off, const void* s
 template <int UNROLL>
 __device__ __noinline__ void push16_mc(char* __restrict__ d, const char* __restrict__ s,
                                        size_t n16, int tid, int nt) {
-  const size_t pass = size_t(nt) * UNROLL;
-  const size_t nmain = n16 / pass * pass;
-  for (size_t i = tid; i < nmain; i += pass) {
+  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
     uint4 v[UNROLL];
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) v[k] = ld_stream_v4(s + ((i + size_t(k) * nt) << 4));
+    for (int k = 0; k < UNROLL; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      if (j < n16) v[k] = ld_stream_v4(s + (j << 4));
+    }
 #pragma unroll
-    for (int k = 0; k < UNROLL; ++k) multimem_st_v4(d + ((i + size_t(k) * nt) << 4), v[k]);
+    for (int k = 0; k < UNROLL; ++k) {
+      const size_t j = i + size_t(k) * nt;
+      if (j < n16) multimem_st_v4(d + (j << 4), v[k]);
+    }
   }
-  for (size_t i = nmain + tid; i < n16; i += nt)
-    multimem_st_v4(d + (i << 4), ld_stream_v4(s + (i << 4)));
 }
 
 template <int LD, int UNROLL>

@@ -2,6 +2,7 @@
 // PDCC_HAS_WIDE (16-bit floats: also build the fp32-output variant) defined. One
 // translation unit per dtype keeps the nvcc jobs parallel.
 #include "ll.cuh"
+#include "sym.cuh"
 
 namespace pdcc {
 
@@ -34,6 +35,24 @@ KernelFn pick_op(int redop, int ar_algo) {
   }
 }
 }  // namespace
+
+namespace {
+template <typename T, int OP>
+SymKernelFn sym_pick(bool rooted) {
+  if constexpr (MmFor<T, OP>::kind == MM_NONE) return nullptr;
+  else return rooted ? sym_reduce_kernel<T, OP, true> : sym_reduce_kernel<T, OP, false>;
+}
+}  // namespace
+
+PDCC_DECLARE_SYM_TABLE(PDCC_SYM_NAME) {
+  using T = PDCC_T;
+  switch (redop) {
+    case PDCC_SUM: return sym_pick<T, PDCC_SUM>(rooted);
+    case PDCC_MIN: return sym_pick<T, PDCC_MIN>(rooted);
+    case PDCC_MAX: return sym_pick<T, PDCC_MAX>(rooted);
+    default: return nullptr;  // PRODUCT: the switch cannot multiply
+  }
+}
 
 PDCC_DECLARE_REDUCE_TABLE(PDCC_NAME) {
   using T = PDCC_T;

@@ -44,7 +44,20 @@ struct KArgs {
   int ntiles;
   int root;
   float scale;
+  int trace;            // PDCC_TRACE: CTA 0 records a timeline into its ctrl words
 };
+
+__device__ __forceinline__ void trace_event(const Ctx& c, uint32_t kind, uint32_t tile, uint64_t t0,
+                                            uint64_t t1, uint32_t aux0, uint32_t aux1) {
+  const uint32_t i = atomicAdd(c.ctrl + kCtrlTrace, 1u);
+  if (i < uint32_t(kCtrlTraceCap)) {
+    uint32_t* e = c.ctrl + kCtrlTrace + 4 + 8 * i;
+    e[0] = kind; e[1] = tile;
+    e[2] = uint32_t(t0); e[3] = uint32_t(t0 >> 32);
+    e[4] = uint32_t(t1); e[5] = uint32_t(t1 >> 32);
+    e[6] = aux0; e[7] = aux1;
+  }
+}
 
 struct Geo {
   uint64_t bytes, tile_bytes;
@@ -99,80 +112,216 @@ __device__ __forceinline__ void init_ctx(const KArgs& k, Prologue& sh, Ctx& c) {
 }
 
 // Warps per stage from the policy's relative weights. A stage with no work on this rank
-// (weight 0) keeps one warp that only forwards its flag, so the flag chain IN -> MID -> OUT
-// -> slot-free is the same on every rank whatever its role.
+// (weight 0) gets no warps at all: its flag is raised on behalf of the stage before it.
 __device__ __forceinline__ void split_warps(int nwarps, int nstages, const int* w, int* a) {
-  int idle = 0, tot = 0;
-  for (int i = 0; i < nstages; ++i) {
-    if (w[i] <= 0) ++idle;
-    else tot += w[i];
-  }
-  const int avail = nwarps - idle;
+  int tot = 0;
+  for (int i = 0; i < nstages; ++i) tot += w[i] > 0 ? w[i] : 0;
   int used = 0, last = -1;
   for (int i = 0; i < 3; ++i) {
-    if (i >= nstages) a[i] = 0;
-    else if (w[i] <= 0) a[i] = 1;
+    if (i >= nstages || w[i] <= 0) a[i] = 0;
     else {
-      a[i] = avail * w[i] / tot;
+      a[i] = nwarps * w[i] / tot;
       if (a[i] < 1) a[i] = 1;
       used += a[i];
       last = i;
     }
   }
-  if (last >= 0 && avail > used) a[last] += avail - used;
+  if (last >= 0 && nwarps > used) a[last] += nwarps - used;
 }
 
-// The tile pipeline: three (two when the policy has no OUT stage) warp groups, each running
-//   for t in tiles:  wait for what the stage consumes; do the stage; publish its flag
-// on its own. Dependencies, per tile t (g = g0 + t):
+// ---------------------------------------------------------------------------------------
+// The tile pipeline.
+//
+// Dependencies, per tile t (g = g0 + t):
 //   IN(t)   after DONE(t - depth) from all ranks   (first `depth` tiles: after every rank
 //           finished everything that came before this call on this ring)
 //   MID(t)  after READY(g+1) from the ranks that feed me
 //   OUT(t)  after MID(g+1) from all ranks
-// DONE(g+1) is raised by the last stage. IN(t) of every rank precedes READY, which
-// precedes every MID(t) that writes into peers' slots, so the guard taken by IN also
-// covers the slot writes of MID.
+// IN(t) of every rank precedes READY, which precedes every MID(t) that writes into peers'
+// slots, so the guard taken by IN also covers the slot writes of MID.
 //
-// Each stage loop is its own __noinline__ function: the three loops never share live
-// registers, so each gets a full allocation and none of them spills.
+// Publishing a tile costs a system-scope fence, and a MEMBAR.SYS issued while the SM has
+// NVLink stores in flight takes 10-25 us to return (profiles/membar_probe_n2.txt): it waits
+// for every outstanding store of the SM to be acknowledged. Nothing that moves data may sit
+// behind it. So a CTA is
+//
+//   warp 0      admitter   polls the flags every stage is waiting for (24 lanes = 3 stages x
+//                          8 ranks, one pass reads them all), acquires, and admits tiles to
+//                          the worker warps through shared memory. Never blocks.
+//   warp 1      publisher  watches the workers' completion counters; whenever some stage has
+//                          finished more tiles it issues ONE fence and raises every flag
+//                          that became due (all stages, all channels) behind it. The fence
+//                          latency delays flags, never data: ring depth absorbs it.
+//   warps 2..   workers    one group per stage that has work on this rank; a warp runs
+//                          "wait until tile t is admitted; do my share of it; count myself
+//                          done" and goes straight on to tile t+1.
+//
+// Who raises which flag: a stage's flag follows the completion of that stage's workers; the
+// flag of a stage with no work on this rank follows the nearest earlier stage that has work
+// ("my MID(t) is done" is vacuously true the moment my IN(t) is; a rank without an OUT stage
+// is finished with slot t as soon as its MID(t) is).
+//
+// Memory model: remote data -> peer's fence.sys + flag store (release) -> admitter's
+// ld.acquire.sys -> st.release.cta (shared) -> worker's ld.acquire.cta: the worker's loads
+// are causally after the peer's stores. Worker stores -> __syncwarp -> red.release.cta ->
+// publisher's ld.acquire.cta -> fence.acq_rel.sys -> flag store: a release pattern that is
+// cumulative over every worker's stores.
+// ---------------------------------------------------------------------------------------
+struct Roles {
+  bool on[3];  // which stages have work on this rank
+};
+
+struct PipeShared {
+  uint32_t admitted[3];   // tiles the workers of stage s may process (monotonic)
+  uint32_t progress[16];  // per worker warp: tiles it has finished (a stage is as far as its
+                          // slowest warp)
+};
+
 template <class P, int STAGE>
-__device__ __noinline__ void stage_loop(const KArgs* kp, Ctx c, bool work) {
+__device__ __noinline__ void worker_loop(const KArgs* kp, Ctx c, PipeShared* ps, int slot) {
   const KArgs& k = *kp;
-  const uint32_t all = (1u << c.n) - 1u;
   const int T = k.ntiles;
-  const uint32_t g0 = c.g0;
+  const int lane = int(threadIdx.x) & 31;
   P p(k, c);
-  if constexpr (STAGE == 0) {
-    const uint32_t to = p.ready_to();
-    for (int t = 0; t < T; ++t) {
-      const uint32_t need = t < c.depth ? g0 : g0 + uint32_t(t - c.depth) + 1u;
-      group_wait(c, CH_DONE, need, all);
-      if (work) p.in(t);
-      group_post(c, CH_READY, g0 + uint32_t(t) + 1u, to);
+  uint32_t have = 0;
+  const bool tr = k.trace && c.b == 0 && lane == 0;
+  for (int t = 0; t < T; ++t) {
+    uint64_t t0 = 0, t1 = 0;
+    if (tr) t0 = globaltimer_ns();
+    if (lane == 0) {
+      while (have <= uint32_t(t)) {
+        have = ld_acquire_cta_shared(&ps->admitted[STAGE]);
+        if (have <= uint32_t(t)) __nanosleep(40);
+      }
     }
-  } else if constexpr (STAGE == 1) {
-    const uint32_t from = p.ready_from();
-    for (int t = 0; t < T; ++t) {
-      group_wait(c, CH_READY, g0 + uint32_t(t) + 1u, from);
-      if (work) p.mid(t);
-      group_post(c, P::kHasOut ? CH_MID : CH_DONE, g0 + uint32_t(t) + 1u, all);
-    }
-    if (!P::kHasOut && c.tid == 0) c.ctrl[kCtrlEpoch + c.b] = g0 + uint32_t(T);
-  } else {
-    for (int t = 0; t < T; ++t) {
-      group_wait(c, CH_MID, g0 + uint32_t(t) + 1u, all);
-      if (work) p.out(t);
-      group_post(c, CH_DONE, g0 + uint32_t(t) + 1u, all);
-    }
-    if (c.tid == 0) c.ctrl[kCtrlEpoch + c.b] = g0 + uint32_t(T);
+    if (tr) t1 = globaltimer_ns();
+    __syncwarp();
+    if constexpr (STAGE == 0) p.in(t);
+    else if constexpr (STAGE == 1) p.mid(t);
+    else p.out(t);
+    __syncwarp();
+    if (lane == 0) st_release_cta_shared(&ps->progress[slot], uint32_t(t) + 1u);
+    if (tr) trace_event(c, uint32_t(STAGE) | (uint32_t(slot) << 8), uint32_t(t), t0, globaltimer_ns(),
+                        uint32_t(t1 - t0), 0u);
   }
 }
 
 template <class P>
+__device__ __noinline__ void admitter_loop(const KArgs* kp, Ctx c, PipeShared* ps, Roles roles) {
+  const KArgs& k = *kp;
+  constexpr int NS = P::kHasOut ? 3 : 2;
+  const uint32_t all = (1u << c.n) - 1u;
+  const int T = k.ntiles;
+  const int lane = int(threadIdx.x) & 31;
+  const int s = lane >> 3, r = lane & 7;  // lane = (stage, source rank)
+  P p(k, c);
+  const bool stage_on = s < NS && roles.on[s];
+  const uint32_t mask = s == 1 ? p.ready_from() : all;
+  const int chan = s == 0 ? CH_DONE : s == 1 ? CH_READY : CH_MID;
+  const bool active = stage_on && r < c.n && ((mask >> r) & 1u);
+  const uint32_t* flag = c.my_pad + flag_index(chan, c.b, r < c.n ? r : 0);
+  const unsigned grp = 0xffu << (8 * (s < 3 ? s : 0));
+  uint32_t tw = 0, spins = 0;
+  for (;;) {
+    const bool pending = stage_on && tw < uint32_t(T);
+    if (!__any_sync(0xffffffffu, pending)) break;
+    bool ok = true;
+    if (pending && active) {
+      const uint32_t need = s == 0 ? (tw < uint32_t(c.depth) ? c.g0 : c.g0 + tw - uint32_t(c.depth) + 1u)
+                                   : c.g0 + tw + 1u;
+      ok = static_cast<int32_t>(ld_relaxed_sys(flag) - need) >= 0;
+    }
+    const unsigned vote = __ballot_sync(0xffffffffu, ok);
+    const bool go = pending && (vote & grp) == grp;
+    if (go && active) (void)ld_acquire_sys(flag);  // monotonic flag: still >= need
+    __syncwarp();
+    if (go) {
+      ++tw;
+      if (r == 0) {
+        st_release_cta_shared(&ps->admitted[s], tw);
+        if (k.trace && c.b == 0) {
+          const uint64_t now = globaltimer_ns();
+          trace_event(c, 32u + uint32_t(s), tw - 1u, now, now, 0u, 0u);
+        }
+      }
+    }
+    if ((++spins & 0x7ffu) == 0) {
+      const bool late = globaltimer_ns() > c.deadline;
+      if (__any_sync(0xffffffffu, late)) {
+        // Give up waiting: record who we were waiting for, then admit everything so that
+        // the workers run to the end (on garbage) and the publisher still raises our flags;
+        // pdcc_comm_check reports the error. A mismatched collective never hangs the GPU.
+        if (pending && active && !ok) {
+          if (atomicCAS(c.ctrl + kCtrlErr, 0u, 1u) == 0u)
+            c.ctrl[kCtrlErrInfo] = (uint32_t(chan) << 28) | (uint32_t(r) << 24) | ((c.g0 + tw + 1u) & 0xffffffu);
+        }
+        if (stage_on && r == 0) st_release_cta_shared(&ps->admitted[s], uint32_t(T));
+        break;
+      }
+    }
+  }
+}
+
+template <class P>
+__device__ __noinline__ void publisher_loop(const KArgs* kp, Ctx c, PipeShared* ps, Roles roles,
+                                            int nw0, int nw1, int nw2) {
+  if ((threadIdx.x & 31) != 0) return;
+  const KArgs& k = *kp;
+  constexpr bool kOut = P::kHasOut;
+  const uint32_t all = (1u << c.n) - 1u;
+  const uint32_t T = uint32_t(k.ntiles);
+  P p(k, c);
+  const uint32_t to = p.ready_to();
+  const bool in_on = roles.on[0], mid_on = roles.on[1], out_on = kOut && roles.on[2];
+  uint32_t pub0 = 0, pub1 = 0, pub2 = 0;
+  for (;;) {
+    uint32_t d0 = T, d1 = T, d2 = T;  // tiles every worker warp of the stage has finished
+    for (int i = 0; i < nw0; ++i) d0 = min(d0, ld_acquire_cta_shared(&ps->progress[i]));
+    for (int i = 0; i < nw1; ++i) d1 = min(d1, ld_acquire_cta_shared(&ps->progress[nw0 + i]));
+    if (out_on)
+      for (int i = 0; i < nw2; ++i) d2 = min(d2, ld_acquire_cta_shared(&ps->progress[nw0 + nw1 + i]));
+    const bool n0 = in_on && d0 > pub0, n1 = mid_on && d1 > pub1, n2 = out_on && d2 > pub2;
+    if (!(n0 || n1 || n2)) {
+      if ((!in_on || pub0 == T) && (!mid_on || pub1 == T) && (!out_on || pub2 == T)) break;
+      __nanosleep(100);
+      continue;
+    }
+    uint64_t tf = 0;
+    if (k.trace && c.b == 0) tf = globaltimer_ns();
+    fence_acq_rel_sys();  // ONE fence for everything that completed since the last round
+    if (k.trace && c.b == 0)
+      trace_event(c, 16u, 0u, tf, globaltimer_ns(), d0 | (d1 << 10) | (d2 << 20), 0u);
+    if (n0) {
+      const uint32_t v = c.g0 + d0;
+      post_flags(c, CH_READY, v, to);
+      if (kOut && !mid_on) post_flags(c, CH_MID, v, all);
+      if (!mid_on && !out_on) post_flags(c, CH_DONE, v, all);
+      pub0 = d0;
+    }
+    if (n1) {
+      const uint32_t v = c.g0 + d1;
+      if (kOut) post_flags(c, CH_MID, v, all);
+      if (!out_on) post_flags(c, CH_DONE, v, all);
+      pub1 = d1;
+    }
+    if (n2) {
+      post_flags(c, CH_DONE, c.g0 + d2, all);
+      pub2 = d2;
+    }
+  }
+  c.ctrl[kCtrlEpoch + c.b] = c.g0 + T;
+}
+
+constexpr int kControlWarps = 2;
+
+template <class P>
 __device__ __forceinline__ void run_pipeline(const KArgs& k) {
   __shared__ Prologue sh;
+  __shared__ PipeShared ps;
   Ctx c;
-  init_ctx(k, sh, c);
+  if (threadIdx.x < 3) ps.admitted[threadIdx.x] = 0;
+  if (threadIdx.x < 16) ps.progress[threadIdx.x] = 0;
+  init_ctx(k, sh, c);  // contains the barriers that publish the zeroed counters
 
   constexpr int NS = P::kHasOut ? 3 : 2;
   int w[3] = {0, 0, 0};
@@ -182,21 +331,32 @@ __device__ __forceinline__ void run_pipeline(const KArgs& k) {
     w[1] = p.w_mid();
     if constexpr (P::kHasOut) w[2] = p.w_out();
   }
+  // A rank with no work at all still takes part in the flag chain through its IN stage.
+  if (w[0] <= 0 && w[1] <= 0 && w[2] <= 0) w[0] = 1;
   int a[3];
-  split_warps(int(blockDim.x) >> 5, NS, w, a);
+  split_warps((int(blockDim.x) >> 5) - kControlWarps, NS, w, a);
+  const Roles roles{{w[0] > 0, w[1] > 0, w[2] > 0}};
   const int warp = int(threadIdx.x) >> 5;
+  if (warp == 0) {
+    admitter_loop<P>(&k, c, &ps, roles);
+    return;
+  }
+  if (warp == 1) {
+    publisher_loop<P>(&k, c, &ps, roles, a[0], a[1], a[2]);
+    return;
+  }
+  const int ww = warp - kControlWarps;
   int stage, first;
-  if (warp < a[0]) { stage = 0; first = 0; }
-  else if (warp < a[0] + a[1]) { stage = 1; first = a[0]; }
-  else if (warp < a[0] + a[1] + a[2]) { stage = 2; first = a[0] + a[1]; }
-  else return;  // warps beyond the groups (a collective with no work on this rank) leave
-  c.tid = int(threadIdx.x) - first * 32;
+  if (ww < a[0]) { stage = 0; first = 0; }
+  else if (ww < a[0] + a[1]) { stage = 1; first = a[0]; }
+  else if (ww < a[0] + a[1] + a[2]) { stage = 2; first = a[0] + a[1]; }
+  else return;
+  c.tid = int(threadIdx.x) - (first + kControlWarps) * 32;
   c.nt = a[stage] * 32;
   c.bar = 1 + stage;
-  const bool work = w[stage] > 0;
-  if (stage == 0) stage_loop<P, 0>(&k, c, work);
-  else if (stage == 1) stage_loop<P, 1>(&k, c, work);
-  else if constexpr (P::kHasOut) stage_loop<P, 2>(&k, c, work);
+  if (stage == 0) worker_loop<P, 0>(&k, c, &ps, ww);
+  else if (stage == 1) worker_loop<P, 1>(&k, c, &ps, ww);
+  else if constexpr (P::kHasOut) worker_loop<P, 2>(&k, c, &ps, ww);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -342,7 +502,7 @@ __device__ __noinline__ void nvls_units(char* __restrict__ mc, char* __restrict_
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const size_t j = j0 + size_t(u) * nt;
-      v[u] = multimem_ld_reduce_v4<KMM>(mc + ((j < hi ? j : j0) << 4));
+      if (j < hi) v[u] = multimem_ld_reduce_v4<KMM>(mc + (j << 4));  // never a redundant switch read
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -409,20 +569,39 @@ struct ReducePolicy {
     return (ROOTED && !kTwoShot) ? (1u << k.root) : all;
   }
   __device__ __forceinline__ uint32_t ready_from() const {
-    return (ROOTED && !kTwoShot) ? (c.rank == k.root ? all : 0u) : all;
+    if constexpr (ROOTED && !kTwoShot) {
+      if (c.rank != k.root) return 0u;
+      // one-shot push: the root has no IN stage of its own, so it raises no READY
+      return ALGO == AR_ONESHOT_P2P ? all & ~(1u << k.root) : all;
+    } else {
+      return all;
+    }
   }
   // Relative weight of each stage on THIS rank (uniform across the CTA); run_pipeline()
   // sizes the warp groups from these. 0 = the stage has no work here.
   __device__ __forceinline__ int w_in() const {
     return (ROOTED && ALGO == AR_ONESHOT_P2P && c.rank == k.root) ? 0 : 1;
   }
+  // The NVLS stages are lopsided: IN is a local copy (fast), MID is a round trip through
+  // the switch per 16 bytes (latency-bound: it needs most of the warps to keep enough
+  // multimem.ld_reduce in flight; profiles/trace_v4_n8.jsonl: 520 us of MID work against
+  // 139 us of IN with equal groups), OUT a local copy again.
   __device__ __forceinline__ int w_mid() const {
-    if constexpr (!ROOTED) return ALGO == AR_ONESHOT_NVLS ? 2 : 1;
-    else if constexpr (ALGO == AR_TWOSHOT_P2P) return c.rank != k.root ? 1 : 0;  // owners
-    else if constexpr (ALGO == AR_TWOSHOT_NVLS) return 1;
-    else return c.rank == k.root ? (ALGO == AR_ONESHOT_NVLS ? 3 : 1) : 0;
+    if constexpr (kNvls) {
+      if constexpr (ROOTED && ALGO == AR_ONESHOT_NVLS) return c.rank == k.root ? 4 : 0;
+      return 4;
+    } else if constexpr (!ROOTED) {
+      return 1;
+    } else if constexpr (ALGO == AR_TWOSHOT_P2P) {
+      return c.rank != k.root ? 1 : 0;  // owners
+    } else {
+      return c.rank == k.root ? 1 : 0;
+    }
   }
-  __device__ __forceinline__ int w_out() const { return (!ROOTED || c.rank == k.root) ? 1 : 0; }
+  __device__ __forceinline__ int w_out() const {
+    if (ROOTED && c.rank != k.root) return 0;
+    return kNvls ? 2 : 1;
+  }
   // Two-shot P2P ownership. all_reduce: every rank owns one chunk of the tile. Rooted
   // reduce: only the n-1 NON-root ranks own chunks, so the root receives each reduced
   // chunk exactly once and nothing else: S bytes in, S bytes out on every GPU, instead of
@@ -462,6 +641,12 @@ struct ReducePolicy {
       }
     } else {  // two-shot P2P: my partial of each chunk goes to the chunk's owner
       const size_t sub = sub_bytes();
+      if (aligned16(src) && (len & 15u) == 0) {
+        // one streaming loop over the tile; chunk o lands in A[me] of its owner's slot
+        deal16<8>(c.a->comm.base, kRootOwnsNothing ? k.root + 1 : 0, c.n, c.rank,
+                  so + size_t(c.rank) * sub, 0, src, size_t(len >> 4), sub >> 4, c.tid, c.nt);
+        return;
+      }
       for (int i = 1; i < c.n; ++i) {
         const int p = (c.rank + i) % c.n;
         if (!is_owner(p)) continue;
@@ -713,14 +898,14 @@ struct MovePolicy {
   // relative weight of each stage on THIS rank (0 = no work here), see run_pipeline()
   __device__ __forceinline__ int w_in() const {
     if constexpr (kTwoPhase || kRootSends) return c.rank == k.root ? 1 : 0;
-    else return KIND != MV_BARRIER ? 1 : 0;
+    else return 1;  // barrier: the IN group only raises READY
   }
   __device__ __forceinline__ int w_mid() const {
     if constexpr (kTwoPhase || kRootSends) return c.rank != k.root ? 1 : 0;
     else if constexpr (KIND == MV_GATHER) return c.rank == k.root ? 3 : 0;
     else if constexpr (KIND == MV_ALLGATHER_PULL) return 3;
     else if constexpr (KIND == MV_ALLGATHER_NVLS) return 2;
-    else return KIND != MV_BARRIER ? 1 : 0;
+    else return 1;  // barrier: the MID group waits for everybody's READY
   }
   __device__ __forceinline__ int w_out() const { return (kTwoPhase && c.rank != k.root) ? 1 : 0; }
 
@@ -745,6 +930,12 @@ struct MovePolicy {
       if (c.rank != k.root) return;
       const char* src = static_cast<const char*>(c.a->in) + off;
       const size_t sub = sub_bytes();
+      if (aligned16(src) && (len & 15u) == 0) {
+        // one streaming loop over the tile; shard o lands at the same offset of its owner's slot
+        deal16<8>(c.a->comm.base, k.root + 1, c.n, k.root, so, sub, src, size_t(len >> 4), sub >> 4,
+                  c.tid, c.nt);
+        return;
+      }
       for (int i = 1; i < c.n; ++i) {
         const int j = (c.rank + i) % c.n;
         const int o = own_index(j);

@@ -12,6 +12,8 @@
 #include <mutex>
 
 #include "ll.cuh"
+#define PDCC_SYM_MOVERS
+#include "sym.cuh"
 #include "tma_copy.cuh"
 
 namespace pdcc {
@@ -98,9 +100,10 @@ struct PlanEnv {
   int max_ctas;           // PDCC_MAX_CTAS          hard cap on CTAs per call (0 = none)
   int default_ctas;       // PDCC_DEFAULT_CTAS      cap below 8 MiB (0 = 128; >0 also caps big ones)
   int tile_bytes;         // PDCC_TILE_BYTES        payload per CTA per tile (0 = table)
-  int depth;              // PDCC_DEPTH             max slots per ring (0 = 8)
+  int depth;              // PDCC_DEPTH             max slots per ring (0 = 16)
   int threads;            // PDCC_THREADS           threads per CTA of the pipeline kernels (0 = auto)
   int copy_tma;           // PDCC_COPY_TMA          local copies through the TMA engine (default 1)
+  int trace;              // PDCC_TRACE             CTA 0 records a timeline (pdcc_comm_read_trace)
 };
 static PlanEnv g_plan_env;
 static std::atomic<int> g_plan_env_state{0};  // 0 = not read, 1 = valid
@@ -116,6 +119,7 @@ static void read_plan_env(PlanEnv* e) {
   e->depth = env_int("PDCC_DEPTH", 0);
   e->threads = env_int("PDCC_THREADS", 0);
   e->copy_tma = env_int("PDCC_COPY_TMA", 1);
+  e->trace = env_int("PDCC_TRACE", 0);
 }
 
 static const PlanEnv& plan_env() {
@@ -134,7 +138,8 @@ static const PlanEnv& plan_env() {
 // Measured table (profiles/): see DESIGN.md §4 "tiles".
 static uint64_t default_tile(int coll, int algo, int n, uint64_t bytes) {
   (void)coll; (void)algo; (void)n;
-  if (bytes >= (uint64_t(64) << 20)) return 64 << 10;
+  if (bytes >= (uint64_t(64) << 20)) return 128 << 10;
+  if (bytes >= (uint64_t(8) << 20)) return 64 << 10;
   return 32 << 10;
 }
 
@@ -330,7 +335,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   uint64_t want = pe.tile_bytes > 0 ? uint64_t(pe.tile_bytes) : default_tile(op.coll, algo, n, bytes);
   uint64_t tile = per_cta < want ? per_cta : want;
   tile = round_up(tile, align);
-  const int max_depth = pe.depth > 0 ? pe.depth : 8;
+  const int max_depth = pe.depth > 0 ? pe.depth : 16;
   int depth = 1;
   uint64_t slot = 0;
   for (int d = max_depth; d >= 1; d >>= 1) {
@@ -381,6 +386,7 @@ int launch_collective(const RankArgs* ranks, int nlocal, const RankArgs* dev_ran
   k.depth = plan.depth;
   k.slot_stride = plan.slot_stride;
   k.root = op.root;
+  k.trace = plan_env().trace;
   k.scale = op.scale == 0.0f ? 1.0f : op.scale;
   if (op.redop == PDCC_AVG) k.scale *= 1.0f / float(n);
 
@@ -491,6 +497,109 @@ int upload_rank_args(const RankArgs* host, int n, RankArgs* dev, void* stream) {
     set_error("uploading per-rank arguments: %s", cudaGetErrorString(e));
     return PDCC_ECUDA;
   }
+  return PDCC_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// Zero-copy collectives on symmetric memory (sym.cuh)
+// ---------------------------------------------------------------------------------------
+SymKernelFn sym_reduce_kernel_for(int dtype, int redop, bool rooted) {
+  switch (dtype) {
+    case PDCC_F32: return sym_table_f32(redop, rooted);
+    case PDCC_BF16: return sym_table_bf16(redop, rooted);
+    case PDCC_F16: return sym_table_f16(redop, rooted);
+    case PDCC_F64: return sym_table_f64(redop, rooted);
+    case PDCC_I32: return sym_table_i32(redop, rooted);
+    case PDCC_I64: return sym_table_i64(redop, rooted);
+    case PDCC_U8: return sym_table_u8(redop, rooted);
+    default: return nullptr;
+  }
+}
+
+uint64_t sym_min_bytes(int nranks) {
+  const PlanEnv& pe = plan_env();
+  return uint64_t(pe.ll_max >= 0 ? pe.ll_max : (512 << 10) / (nranks > 0 ? nranks : 1));
+}
+
+bool sym_supported(int coll, int dtype, int redop) {
+  if (redop == PDCC_AVG) redop = PDCC_SUM;
+  switch (coll) {
+    case PDCC_ALL_REDUCE: return sym_reduce_kernel_for(dtype, redop, false) != nullptr;
+    case PDCC_REDUCE: return sym_reduce_kernel_for(dtype, redop, true) != nullptr;
+    case PDCC_BROADCAST: case PDCC_ALL_GATHER: return true;
+    default: return false;
+  }
+}
+
+int launch_sym(const DevComm& comm, int ring_limit, const pdcc_op_t& op, const SymTensor& in,
+               const SymTensor& out, void* stream) {
+  const int n = comm.nranks;
+  const uint64_t bytes = op.count * dtype_size(op.dtype);
+  if (comm.mc == nullptr || (bytes & 15u) != 0 || bytes == 0) {
+    set_error("zero-copy path needs a multicast mapping and a multiple of 16 bytes");
+    return PDCC_EINVAL;
+  }
+  if (ring_limit <= 0 || ring_limit > PDCC_MAX_BLOCKS) ring_limit = PDCC_MAX_BLOCKS;
+  SymArgs a;
+  memset(&a, 0, sizeof(a));
+  a.comm = comm;
+  a.in_local = in.local;
+  a.in_mc = in.mc;
+  a.out_local = out.local;
+  a.out_mc = out.mc;
+  for (int p = 0; p < PDCC_MAX_RANKS; ++p) a.out_peer[p] = out.peer[p];
+  a.bytes = bytes;
+  a.root = op.root;
+  a.scale = op.scale == 0.0f ? 1.0f : op.scale;
+  if (op.redop == PDCC_AVG) a.scale *= 1.0f / float(n);
+  const PlanEnv& pe = plan_env();
+
+  SymKernelFn fn = nullptr;
+  uint64_t work = bytes;  // bytes one rank moves: sizes the grid
+  switch (op.coll) {
+    case PDCC_ALL_REDUCE:
+      fn = sym_reduce_kernel_for(op.dtype, op.redop == PDCC_AVG ? PDCC_SUM : op.redop, false);
+      work = bytes / n;
+      break;
+    case PDCC_REDUCE:
+      fn = sym_reduce_kernel_for(op.dtype, op.redop == PDCC_AVG ? PDCC_SUM : op.redop, true);
+      work = bytes / n;
+      break;
+    case PDCC_ALL_GATHER: fn = sym_all_gather_kernel; break;
+    case PDCC_BROADCAST: {
+      const uint64_t big = uint64_t(pe.rooted_twoshot_min);
+      if (n > 2 && bytes >= big && op.algo != PDCC_ALGO_NVLS) {
+        fn = sym_broadcast2_kernel;
+        const uint64_t align = 16 * uint64_t(n - 1);
+        uint64_t tile = pe.tile_bytes > 0 ? uint64_t(pe.tile_bytes) : (uint64_t(128) << 10);
+        a.tile_bytes = (tile + align - 1) / align * align;
+      } else {
+        fn = sym_broadcast_kernel;
+      }
+      break;
+    }
+    default: break;
+  }
+  if (!fn) {
+    set_error("no zero-copy kernel for collective %d dtype %d op %d", op.coll, op.dtype, op.redop);
+    return PDCC_EUNSUPPORTED;
+  }
+  int nb = op.nblocks > 0 ? op.nblocks : int(ceil_div(work, uint64_t(16) << 10));
+  int cap = pe.max_ctas > 0 ? pe.max_ctas : ring_limit;
+  if (cap > ring_limit) cap = ring_limit;
+  if (nb > cap) nb = cap;
+  if (nb < 1) nb = 1;
+  if (fn == sym_broadcast2_kernel) {
+    const uint64_t tiles = ceil_div(bytes, a.tile_bytes);
+    if (uint64_t(nb) > tiles) nb = int(tiles);
+  }
+  fn<<<dim3(nb), dim3(kThreads), 0, static_cast<cudaStream_t>(stream)>>>(a);
+  cudaError_t err = cudaGetLastError();
+  if (err != cudaSuccess) {
+    set_error("zero-copy kernel launch failed: %s", cudaGetErrorString(err));
+    return PDCC_ECUDA;
+  }
+  g_launches.fetch_add(1, std::memory_order_relaxed);
   return PDCC_OK;
 }
 

@@ -259,8 +259,28 @@ struct Mapping {
   bool have_handle = false;
 };
 
+// One symmetric allocation: the same number of bytes on every rank, every rank's copy
+// mapped into this process, and (where the box allows) one multicast alias over all of
+// them. The communicator's own block is region 0; pdcc_sym_alloc adds more.
+struct Region {
+  size_t bytes = 0;
+  Mapping peers[PDCC_MAX_RANKS];  // POSIX-fd path
+  Mapping mc;
+  bool has_mc = false;
+  void* legacy_base = nullptr;    // cudaMalloc'd (legacy IPC / local)
+  void* legacy_peer[PDCC_MAX_RANKS] = {};
+  char* base[PDCC_MAX_RANKS] = {};  // base[p] = local VA of rank p's copy
+  char* mcp = nullptr;              // multicast alias (nullptr: none)
+};
+
+constexpr int kMaxRegions = 64;
+
 struct pdcc_comm {
   pdcc_comm_config_t cfg{};
+  pdcc_store_t* store = nullptr;   // kept for later symmetric allocations (caller owns it)
+  bool want_mc = false;            // every rank reported multicast support
+  Region* regions[kMaxRegions] = {};
+  int nregions = 0;                // region counter doubles as the store-key suffix
   int kind = PDCC_HANDLE_LOCAL;
   int sm_count = 0;
   int max_blocks = PDCC_MAX_BLOCKS;
@@ -269,10 +289,7 @@ struct pdcc_comm {
   size_t block_bytes = 0;
   size_t heap_off = 0;
   bool has_mc = false;
-  Mapping peers[PDCC_MAX_RANKS];  // POSIX-fd path
-  Mapping mc;
-  void* legacy_base = nullptr;  // cudaMalloc'd block (legacy IPC / local)
-  void* legacy_peer[PDCC_MAX_RANKS] = {};
+  Region blk;  // the communicator's own block (ctrl, pads, LL slots, rings, heap)
   DevComm dev{};
 };
 
@@ -395,11 +412,8 @@ static int fill_dev(pdcc_comm* c) {
   c->dev.ring_bytes = uint32_t(c->ring_bytes);
   c->dev.timeout_ms = uint32_t(c->cfg.device_timeout_ms > 0 ? c->cfg.device_timeout_ms : 10000);
   for (int p = 0; p < PDCC_MAX_RANKS; ++p) c->dev.base[p] = nullptr;
-  for (int p = 0; p < c->cfg.nranks; ++p) {
-    if (c->kind == PDCC_HANDLE_POSIX_FD) c->dev.base[p] = reinterpret_cast<char*>(c->peers[p].va);
-    else c->dev.base[p] = static_cast<char*>(c->legacy_peer[p]);
-  }
-  c->dev.mc = c->has_mc ? reinterpret_cast<char*>(c->mc.va) : nullptr;
+  for (int p = 0; p < c->cfg.nranks; ++p) c->dev.base[p] = c->blk.base[p];
+  c->dev.mc = c->has_mc ? c->blk.mcp : nullptr;
   return PDCC_OK;
 }
 
@@ -415,23 +429,58 @@ static void sizes_from_cfg(pdcc_comm* c) {
   c->block_bytes = c->heap_off + c->cfg.heap_bytes;
 }
 
+static void region_release(pdcc_comm* c, Region* rg) {
+  if (c->kind == PDCC_HANDLE_POSIX_FD) {
+    unmap(rg->mc);
+    for (int p = 0; p < c->cfg.nranks; ++p) unmap(rg->peers[p]);
+  } else {
+    for (int p = 0; p < c->cfg.nranks; ++p)
+      if (p != c->cfg.rank && rg->legacy_peer[p]) cudaIpcCloseMemHandle(rg->legacy_peer[p]);
+    if (rg->legacy_base) cudaFree(rg->legacy_base);
+    rg->legacy_base = nullptr;
+  }
+}
+
 int pdcc_comm_destroy(pdcc_comm_t* c) {
   if (!c) return PDCC_EINVAL;
   cudaSetDevice(c->cfg.device);
   cudaDeviceSynchronize();
-  if (c->kind == PDCC_HANDLE_POSIX_FD) {
-    unmap(c->mc);
-    for (int p = 0; p < c->cfg.nranks; ++p) unmap(c->peers[p]);
-  } else {
-    for (int p = 0; p < c->cfg.nranks; ++p)
-      if (p != c->cfg.rank && c->legacy_peer[p]) cudaIpcCloseMemHandle(c->legacy_peer[p]);
-    if (c->legacy_base) cudaFree(c->legacy_base);
+  for (int i = 0; i < c->nregions; ++i) {
+    if (c->regions[i]) {
+      region_release(c, c->regions[i]);
+      delete c->regions[i];
+    }
   }
+  region_release(c, &c->blk);
   delete c;
   return PDCC_OK;
 }
 
-static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
+// Closes a set of file descriptors on every exit path.
+struct FdBag {
+  std::vector<int> fds;
+  int add(int fd) {
+    if (fd >= 0) fds.push_back(fd);
+    return fd;
+  }
+  void close_one(int fd) {
+    for (auto& f : fds)
+      if (f == fd && fd >= 0) {
+        ::close(f);
+        f = -1;
+      }
+  }
+  ~FdBag() {
+    for (int f : fds)
+      if (f >= 0) ::close(f);
+  }
+};
+
+// Builds region `rg` (rg->bytes requested, rounded up to the allocation / multicast
+// granularity): my copy, every peer's copy mapped here, and the multicast alias when
+// want_mc and every rank manages to bind. `tag` namespaces the store keys and the socket
+// name, so any number of regions can be built one after another on one communicator.
+static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc, Region* rg, const char* tag) {
   const Driver& d = drv();
   const pdcc_comm_config_t& cfg = c->cfg;
   const int n = cfg.nranks, me = cfg.rank, tmo = cfg.timeout_ms;
@@ -446,34 +495,36 @@ static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
   CUmulticastObjectProp mp{};
   if (want_mc) {
     mp.numDevices = unsigned(n);
-    mp.size = c->block_bytes;
+    mp.size = rg->bytes;
     mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
     size_t mg = 0;
     if (d.p_cuMulticastGetGranularity(&mg, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED) ==
             CUDA_SUCCESS && mg > gran)
       gran = mg;
   }
-  c->block_bytes = round_up_sz(c->block_bytes, gran);
-  mp.size = c->block_bytes;
+  rg->bytes = round_up_sz(rg->bytes, gran);
+  mp.size = rg->bytes;
 
   // my block
-  Mapping& mine = c->peers[me];
-  CU_TRY(cuMemCreate(&mine.handle, c->block_bytes, &ap, 0));
+  Mapping& mine = rg->peers[me];
+  CU_TRY(cuMemCreate(&mine.handle, rg->bytes, &ap, 0));
   mine.have_handle = true;
+  FdBag bag;  // every early return below closes what is still open
   int my_fd = -1;
   CU_TRY(cuMemExportToShareableHandle(&my_fd, mine.handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR,
                                       0));
+  bag.add(my_fd);
 
   // listener, published in the store
   char sname[160];
-  snprintf(sname, sizeof(sname), "pdcc-%s-%d-%d", cfg.key, me, int(getpid()));
+  snprintf(sname, sizeof(sname), "pdcc-%s-%s%d-%d", cfg.key, tag, me, int(getpid()));
   int lsock = make_listener(sname);
   if (lsock < 0) {
     set_error("cannot bind unix socket %s: %s", sname, strerror(errno));
-    ::close(my_fd);
     return PDCC_ESYS;
   }
-  int rc = pdcc_store_set(st, skey(cfg, "sock", me).c_str(), sname, int(strlen(sname)));
+  bag.add(lsock);
+  int rc = pdcc_store_set(st, skey(cfg, (std::string(tag) + "sock").c_str(), me).c_str(), sname, int(strlen(sname)));
   if (rc) return rc;
 
   // receive in a helper thread while this thread sends
@@ -486,7 +537,7 @@ static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
     const int p = (me + i) % n;
     char pname[160] = {0};
     int len = 0;
-    rc = pdcc_store_get(st, skey(cfg, "sock", p).c_str(), pname, sizeof(pname) - 1, &len, tmo);
+    rc = pdcc_store_get(st, skey(cfg, (std::string(tag) + "sock").c_str(), p).c_str(), pname, sizeof(pname) - 1, &len, tmo);
     if (rc) {
       send_ok = false;
       break;
@@ -499,65 +550,58 @@ static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
     if (s >= 0) ::close(s);
   }
   rx.join();
-  ::close(my_fd);
+  bag.close_one(my_fd);
+  for (int p = 0; p < n; ++p) bag.add(fds[p]);
   if (!send_ok || !recv_ok) {
     set_error("fd exchange failed (%s%s)", send_ok ? "" : send_err.c_str(),
               recv_ok ? "" : " receive timed out");
-    ::close(lsock);
     return PDCC_ESYS;
   }
 
   // map every block (mine included) into this process
-  rc = map_handle(mine, c->block_bytes, cfg.device);
+  rc = map_handle(mine, rg->bytes, cfg.device);
   if (rc) return rc;
   for (int p = 0; p < n; ++p) {
     if (p == me) continue;
-    Mapping& m = c->peers[p];
+    Mapping& m = rg->peers[p];
     CUresult r = d.p_cuMemImportFromShareableHandle(
         &m.handle, reinterpret_cast<void*>(static_cast<uintptr_t>(fds[p])),
         CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
-    ::close(fds[p]);
+    bag.close_one(fds[p]);
     if (r != CUDA_SUCCESS) {
       set_error("cuMemImportFromShareableHandle(rank %d): %s", p, cu_err(r));
-      ::close(lsock);
       return PDCC_ECUDA;
     }
     m.have_handle = true;
-    rc = map_handle(m, c->block_bytes, cfg.device);
-    if (rc) {
-      ::close(lsock);
-      return rc;
-    }
+    rc = map_handle(m, rg->bytes, cfg.device);
+    if (rc) return rc;
   }
 
   // Nobody may still be collecting memory handles when rank 0 starts handing out the
   // multicast handle on the same sockets.
-  rc = pdcc_store_barrier(st, skey(cfg, "memx").c_str(), n, tmo);
-  if (rc) {
-    ::close(lsock);
-    return rc;
-  }
+  rc = pdcc_store_barrier(st, skey(cfg, (std::string(tag) + "memx").c_str()).c_str(), n, tmo);
+  if (rc) return rc;
 
   // ---- multicast: every step is voted on so that all ranks agree on has_mc ----------
-  c->has_mc = false;
+  rg->has_mc = false;
   if (want_mc) {
     int ok = 1;
     CUdevice cudev = 0;
     if (d.p_cuDeviceGet(&cudev, cfg.device) != CUDA_SUCCESS) ok = 0;
     if (me == 0) {
       int mfd = -1;
-      if (ok && d.p_cuMulticastCreate(&c->mc.handle, &mp) != CUDA_SUCCESS) ok = 0;
-      if (ok) c->mc.have_handle = true;
-      if (ok && d.p_cuMemExportToShareableHandle(&mfd, c->mc.handle,
+      if (ok && d.p_cuMulticastCreate(&rg->mc.handle, &mp) != CUDA_SUCCESS) ok = 0;
+      if (ok) rg->mc.have_handle = true;
+      if (ok && d.p_cuMemExportToShareableHandle(&mfd, rg->mc.handle,
                                                  CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR,
                                                  0) != CUDA_SUCCESS)
         ok = 0;
-      store_put_int(st, skey(cfg, "mc_created"), ok);
+      store_put_int(st, skey(cfg, (std::string(tag) + "mc_created").c_str()), ok);
       if (ok) {
         for (int p = 1; p < n; ++p) {
           char pname[160] = {0};
           int len = 0;
-          if (pdcc_store_get(st, skey(cfg, "sock", p).c_str(), pname, sizeof(pname) - 1, &len,
+          if (pdcc_store_get(st, skey(cfg, (std::string(tag) + "sock").c_str(), p).c_str(), pname, sizeof(pname) - 1, &len,
                              tmo))
             continue;
           int s = connect_to(std::string(pname, size_t(len)), tmo);
@@ -570,7 +614,7 @@ static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
       }
     } else {
       int created = 0;
-      if (store_get_int(st, skey(cfg, "mc_created"), &created, tmo) != PDCC_OK) created = 0;
+      if (store_get_int(st, skey(cfg, (std::string(tag) + "mc_created").c_str()), &created, tmo) != PDCC_OK) created = 0;
       if (!created) {
         ok = 0;
       } else {
@@ -579,73 +623,76 @@ static int create_posix(pdcc_comm* c, pdcc_store_t* st, bool want_mc) {
           ok = 0;
         } else {
           if (d.p_cuMemImportFromShareableHandle(
-                  &c->mc.handle, reinterpret_cast<void*>(static_cast<uintptr_t>(mfds[0])),
+                  &rg->mc.handle, reinterpret_cast<void*>(static_cast<uintptr_t>(mfds[0])),
                   CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR) != CUDA_SUCCESS)
             ok = 0;
           else
-            c->mc.have_handle = true;
+            rg->mc.have_handle = true;
           ::close(mfds[0]);
         }
       }
     }
-    if (ok && d.p_cuMulticastAddDevice(c->mc.handle, cudev) != CUDA_SUCCESS) ok = 0;
+    if (ok && d.p_cuMulticastAddDevice(rg->mc.handle, cudev) != CUDA_SUCCESS) ok = 0;
     // vote 1: everyone added its device (binding before that is an error)
-    store_put_int(st, skey(cfg, "mc_add", me), ok);
+    store_put_int(st, skey(cfg, (std::string(tag) + "mc_add").c_str(), me), ok);
     for (int p = 0; p < n; ++p) {
       int v = 0;
-      if (store_get_int(st, skey(cfg, "mc_add", p), &v, tmo) != PDCC_OK || !v) ok = 0;
+      if (store_get_int(st, skey(cfg, (std::string(tag) + "mc_add").c_str(), p), &v, tmo) != PDCC_OK || !v) ok = 0;
     }
-    if (ok && d.p_cuMulticastBindMem(c->mc.handle, 0, mine.handle, 0, c->block_bytes, 0) !=
+    if (ok && d.p_cuMulticastBindMem(rg->mc.handle, 0, mine.handle, 0, rg->bytes, 0) !=
                   CUDA_SUCCESS)
       ok = 0;
     if (ok) {
-      c->mc.size = c->block_bytes;
-      if (d.p_cuMemAddressReserve(&c->mc.va, c->block_bytes, gran, 0, 0) != CUDA_SUCCESS) {
+      rg->mc.size = rg->bytes;
+      if (d.p_cuMemAddressReserve(&rg->mc.va, rg->bytes, gran, 0, 0) != CUDA_SUCCESS) {
         ok = 0;
-        c->mc.va = 0;
+        rg->mc.va = 0;
       }
     }
     if (ok) {
-      if (d.p_cuMemMap(c->mc.va, c->block_bytes, 0, c->mc.handle, 0) != CUDA_SUCCESS) ok = 0;
-      else c->mc.mapped = true;
+      if (d.p_cuMemMap(rg->mc.va, rg->bytes, 0, rg->mc.handle, 0) != CUDA_SUCCESS) ok = 0;
+      else rg->mc.mapped = true;
     }
     if (ok) {
       CUmemAccessDesc acc{};
       acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
       acc.location.id = cfg.device;
       acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
-      if (d.p_cuMemSetAccess(c->mc.va, c->block_bytes, &acc, 1) != CUDA_SUCCESS) ok = 0;
+      if (d.p_cuMemSetAccess(rg->mc.va, rg->bytes, &acc, 1) != CUDA_SUCCESS) ok = 0;
     }
     // vote 2: everyone bound and mapped
-    store_put_int(st, skey(cfg, "mc_bound", me), ok);
+    store_put_int(st, skey(cfg, (std::string(tag) + "mc_bound").c_str(), me), ok);
     for (int p = 0; p < n; ++p) {
       int v = 0;
-      if (store_get_int(st, skey(cfg, "mc_bound", p), &v, tmo) != PDCC_OK || !v) ok = 0;
+      if (store_get_int(st, skey(cfg, (std::string(tag) + "mc_bound").c_str(), p), &v, tmo) != PDCC_OK || !v) ok = 0;
     }
-    c->has_mc = ok != 0;
-    if (!c->has_mc) unmap(c->mc);
+    rg->has_mc = ok != 0;
+    if (!rg->has_mc) unmap(rg->mc);
   }
-  ::close(lsock);
+  for (int p = 0; p < n; ++p) rg->base[p] = reinterpret_cast<char*>(rg->peers[p].va);
+  rg->mcp = rg->has_mc ? reinterpret_cast<char*>(rg->mc.va) : nullptr;
   return PDCC_OK;
 }
 
-static int create_legacy(pdcc_comm* c, pdcc_store_t* st) {
+static int create_legacy(pdcc_comm* c, pdcc_store_t* st, Region* rg, const char* tag) {
   const pdcc_comm_config_t& cfg = c->cfg;
   const int n = cfg.nranks, me = cfg.rank, tmo = cfg.timeout_ms;
-  CUDA_TRY(cudaMalloc(&c->legacy_base, c->block_bytes));
-  c->legacy_peer[me] = c->legacy_base;
+  CUDA_TRY(cudaMalloc(&rg->legacy_base, rg->bytes));
+  rg->legacy_peer[me] = rg->legacy_base;
+  rg->base[me] = static_cast<char*>(rg->legacy_base);
   if (n == 1) return PDCC_OK;
   cudaIpcMemHandle_t h;
-  CUDA_TRY(cudaIpcGetMemHandle(&h, c->legacy_base));
-  int rc = pdcc_store_set(st, skey(cfg, "ipc", me).c_str(), &h, sizeof(h));
+  CUDA_TRY(cudaIpcGetMemHandle(&h, rg->legacy_base));
+  int rc = pdcc_store_set(st, skey(cfg, (std::string(tag) + "ipc").c_str(), me).c_str(), &h, sizeof(h));
   if (rc) return rc;
   for (int p = 0; p < n; ++p) {
     if (p == me) continue;
     cudaIpcMemHandle_t ph;
     int len = 0;
-    rc = pdcc_store_get(st, skey(cfg, "ipc", p).c_str(), &ph, sizeof(ph), &len, tmo);
+    rc = pdcc_store_get(st, skey(cfg, (std::string(tag) + "ipc").c_str(), p).c_str(), &ph, sizeof(ph), &len, tmo);
     if (rc) return rc;
-    CUDA_TRY(cudaIpcOpenMemHandle(&c->legacy_peer[p], ph, cudaIpcMemLazyEnablePeerAccess));
+    CUDA_TRY(cudaIpcOpenMemHandle(&rg->legacy_peer[p], ph, cudaIpcMemLazyEnablePeerAccess));
+    rg->base[p] = static_cast<char*>(rg->legacy_peer[p]);
   }
   return PDCC_OK;
 }
@@ -670,13 +717,15 @@ int pdcc_comm_create(pdcc_store_t* st, const pdcc_comm_config_t* cfg_in, pdcc_co
 
   auto* c = new pdcc_comm();
   c->cfg = cfg;
+  c->store = st;
   c->sm_count = caps.sm_count;
   sizes_from_cfg(c);
+  c->blk.bytes = c->block_bytes;
 
   const int n = cfg.nranks, me = cfg.rank;
   if (n == 1) {
     c->kind = PDCC_HANDLE_LOCAL;
-    rc = create_legacy(c, st);
+    rc = create_legacy(c, st, &c->blk, "");
   } else {
     // agree on the handle kind: everyone publishes what it can do
     int mine[2] = {caps.vmm_supported && caps.posix_fd_supported && drv().ok,
@@ -696,13 +745,16 @@ int pdcc_comm_create(pdcc_store_t* st, const pdcc_comm_config_t* cfg_in, pdcc_co
     if (rc == PDCC_OK) {
       if (all_posix) {
         c->kind = PDCC_HANDLE_POSIX_FD;
-        rc = create_posix(c, st, all_mc);
+        c->want_mc = all_mc;
+        rc = create_posix(c, st, all_mc, &c->blk, "");
+        c->has_mc = c->blk.has_mc;
+        c->block_bytes = c->blk.bytes;
       } else if (cfg.handle_kind == PDCC_HANDLE_POSIX_FD) {
         set_error("POSIX fd handles requested but not supported on every rank");
         rc = PDCC_EUNSUPPORTED;
       } else {
         c->kind = PDCC_HANDLE_LEGACY_IPC;
-        rc = create_legacy(c, st);
+        rc = create_legacy(c, st, &c->blk, "");
       }
     }
     if (rc == PDCC_OK && cfg.multicast == 1 && !c->has_mc) {
@@ -738,6 +790,12 @@ int pdcc_comm_create(pdcc_store_t* st, const pdcc_comm_config_t* cfg_in, pdcc_co
   return PDCC_OK;
 }
 
+// CTAs of one call must all be resident (they wait on their peers): one per SM.
+static int ring_limit(const pdcc_comm* c) {
+  const int resident = c->sm_count > 0 ? c->sm_count * PDCC_MIN_CTAS_PER_SM_HOST : c->max_blocks;
+  return c->max_blocks < resident ? c->max_blocks : resident;
+}
+
 int pdcc_comm_info(pdcc_comm_t* c, pdcc_comm_info_t* info) {
   if (!c || !info) return PDCC_EINVAL;
   memset(info, 0, sizeof(*info));
@@ -770,17 +828,29 @@ static int check_block(char* base, int rank) {
   return PDCC_OK;
 }
 
+// Copies the timeline CTA 0 recorded (PDCC_TRACE=1) to `out` (8 uint32 per event) and
+// clears it. Synchronises the device. *count = events recorded (may exceed cap: truncated).
+int pdcc_comm_read_trace(pdcc_comm_t* c, uint32_t* out, int cap_events, int* count) {
+  if (!c || !out || !count) return PDCC_EINVAL;
+  CUDA_TRY(cudaSetDevice(c->cfg.device));
+  CUDA_TRY(cudaDeviceSynchronize());
+  char* base = c->dev.base[c->cfg.rank];
+  uint32_t n = 0;
+  CUDA_TRY(cudaMemcpy(&n, base + size_t(kCtrlTrace) * 4, 4, cudaMemcpyDeviceToHost));
+  *count = int(n);
+  int take = int(n) < kCtrlTraceCap ? int(n) : kCtrlTraceCap;
+  if (take > cap_events) take = cap_events;
+  if (take > 0)
+    CUDA_TRY(cudaMemcpy(out, base + size_t(kCtrlTrace + 4) * 4, size_t(take) * 32, cudaMemcpyDeviceToHost));
+  CUDA_TRY(cudaMemset(base + size_t(kCtrlTrace) * 4, 0, 4));
+  return PDCC_OK;
+}
+
 int pdcc_comm_check(pdcc_comm_t* c) {
   if (!c) return PDCC_EINVAL;
   CUDA_TRY(cudaSetDevice(c->cfg.device));
   CUDA_TRY(cudaDeviceSynchronize());
   return check_block(c->dev.base[c->cfg.rank], c->cfg.rank);
-}
-
-// CTAs of one call must all be resident (they wait on their peers): one per SM.
-static int ring_limit(const pdcc_comm* c) {
-  const int resident = c->sm_count > 0 ? c->sm_count * PDCC_MIN_CTAS_PER_SM_HOST : c->max_blocks;
-  return c->max_blocks < resident ? c->max_blocks : resident;
 }
 
 int pdcc_plan(pdcc_comm_t* c, const pdcc_op_t* op, int* algo, int* nblocks, int* threads,
@@ -872,6 +942,164 @@ static void fill_rank_args(RankArgs* ra, const DevComm& dev, const pdcc_op_t& op
   for (int j = 0; j < PDCC_MAX_RANKS; ++j) ra->list[j] = op.list[j];
 }
 
+// ---------------------------------------------------------------- symmetric memory ----
+// Collective: every rank of the communicator calls it with the same size, in the same
+// order. The new region is mapped on every rank and (when the communicator has multicast)
+// bound to its own multicast object, so any range of it has a peer address on every rank
+// and one multicast alias. Regions live until the communicator is destroyed.
+int pdcc_sym_alloc(pdcc_comm_t* c, size_t bytes, void** ptr) {
+  if (!c || !ptr || bytes == 0) return PDCC_EINVAL;
+  if (c->nregions >= kMaxRegions) {
+    set_error("at most %d symmetric regions per communicator", kMaxRegions);
+    return PDCC_EINVAL;
+  }
+  CUDA_TRY(cudaSetDevice(c->cfg.device));
+  auto* rg = new Region();
+  rg->bytes = round_up_sz(bytes, size_t(2) << 20);
+  char tag[32];
+  snprintf(tag, sizeof(tag), "sym%d/", c->nregions);
+  int rc;
+  if (c->kind == PDCC_HANDLE_POSIX_FD) rc = create_posix(c, c->store, c->want_mc && c->has_mc, rg, tag);
+  else rc = create_legacy(c, c->store, rg, tag);
+  if (rc == PDCC_OK && c->cfg.nranks > 1) {
+    // nobody may touch the region before every rank has mapped it
+    rc = pdcc_store_barrier(c->store, skey(c->cfg, (std::string(tag) + "ready").c_str()).c_str(),
+                            c->cfg.nranks, c->cfg.timeout_ms);
+  }
+  if (rc != PDCC_OK) {
+    std::string keep = g_err;
+    region_release(c, rg);
+    delete rg;
+    set_error("%s", keep.c_str());
+    return rc;
+  }
+  c->regions[c->nregions++] = rg;
+  *ptr = rg->base[c->cfg.rank];
+  return PDCC_OK;
+}
+
+// The region that holds [p, p + len) entirely, or nullptr.
+static Region* find_region(pdcc_comm* c, const void* p, size_t len, size_t* off) {
+  const char* q = static_cast<const char*>(p);
+  for (int i = 0; i < c->nregions; ++i) {
+    Region* rg = c->regions[i];
+    const char* lo = rg->base[c->cfg.rank];
+    if (q >= lo && q + len <= lo + rg->bytes) {
+      *off = size_t(q - lo);
+      return rg;
+    }
+  }
+  // the heap inside the communicator's own block counts as symmetric memory too
+  if (c->cfg.heap_bytes) {
+    const char* lo = c->blk.base[c->cfg.rank] + c->heap_off;
+    if (q >= lo && q + len <= lo + c->cfg.heap_bytes) {
+      *off = size_t(q - c->blk.base[c->cfg.rank]);
+      return &c->blk;
+    }
+  }
+  return nullptr;
+}
+
+int pdcc_sym_query(pdcc_comm_t* c, const void* ptr, size_t bytes, int* is_symmetric,
+                   int* has_multicast) {
+  if (!c || !ptr) return PDCC_EINVAL;
+  size_t off = 0;
+  Region* rg = find_region(c, ptr, bytes, &off);
+  if (is_symmetric) *is_symmetric = rg != nullptr;
+  if (has_multicast) *has_multicast = rg != nullptr && rg->has_mc;
+  return PDCC_OK;
+}
+
+static void sym_tensor(const pdcc_comm* c, const Region* rg, size_t off, SymTensor* t) {
+  t->local = rg->base[c->cfg.rank] + off;
+  t->mc = rg->mcp ? rg->mcp + off : nullptr;
+  for (int p = 0; p < c->cfg.nranks; ++p) t->peer[p] = rg->base[p] + off;
+}
+
+// Decides whether `op` runs on the zero-copy path and, if so, launches it.
+//   *taken = 1: launched (or failed with the returned code); 0: use the staged path.
+// The decision only depends on things that are the same on every rank under the contract
+// "symmetric on every rank or on none" (sym.cuh): size, dtype, op, and whether THIS rank's
+// tensor is symmetric.
+static int try_symmetric(pdcc_comm* c, const pdcc_op_t& op, void* stream, int* taken) {
+  *taken = 0;
+  const int n = c->cfg.nranks, me = c->cfg.rank;
+  if (n < 2 || !c->has_mc || c->nregions + (c->cfg.heap_bytes ? 1 : 0) == 0) return PDCC_OK;
+  if (op.algo != PDCC_ALGO_AUTO && op.algo != PDCC_ALGO_SYM &&
+      !(op.coll == PDCC_BROADCAST && op.algo == PDCC_ALGO_NVLS))
+    return PDCC_OK;
+  const bool forced = op.algo == PDCC_ALGO_SYM;
+  const uint64_t bytes = op.count * dtype_size(op.dtype);
+  auto refuse = [&](const char* why) {
+    if (!forced) return PDCC_OK;
+    set_error("zero-copy path not applicable: %s", why);
+    return PDCC_EINVAL;
+  };
+  if (op.coll != PDCC_ALL_REDUCE && op.coll != PDCC_REDUCE && op.coll != PDCC_BROADCAST &&
+      op.coll != PDCC_ALL_GATHER)
+    return refuse("collective has no zero-copy kernel");
+  if (!sym_supported(op.coll, op.dtype, op.redop)) return refuse("the switch cannot reduce this dtype/op");
+  if (bytes == 0 || (bytes & 15u)) return refuse("size is not a multiple of 16 bytes");
+  if (op.out_dtype != op.dtype) return refuse("fused cast");
+  auto aligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+
+  SymTensor in, out;
+  size_t off = 0;
+  Region* rg = nullptr;
+  switch (op.coll) {
+    case PDCC_ALL_REDUCE: {
+      if (!aligned(op.in) || !aligned(op.out)) return refuse("tensor not 16-byte aligned");
+      rg = find_region(c, op.in, bytes, &off);
+      if (!rg || !rg->has_mc) return refuse("input is not in multicast-bound symmetric memory");
+      sym_tensor(c, rg, off, &in);
+      rg = find_region(c, op.out, bytes, &off);
+      if (!rg || !rg->has_mc) return refuse("output is not in multicast-bound symmetric memory");
+      sym_tensor(c, rg, off, &out);
+      break;
+    }
+    case PDCC_REDUCE: {
+      if (!aligned(op.in)) return refuse("tensor not 16-byte aligned");
+      rg = find_region(c, op.in, bytes, &off);
+      if (!rg || !rg->has_mc) return refuse("input is not in multicast-bound symmetric memory");
+      if (me == op.root && op.out != op.in) {
+        set_error("reduce on a symmetric tensor is in place on the destination rank");
+        return PDCC_EINVAL;
+      }
+      sym_tensor(c, rg, off, &in);
+      out = in;  // the destination is the root's copy of the same tensor
+      break;
+    }
+    case PDCC_BROADCAST: {
+      const void* t = me == op.root ? op.in : op.out;
+      if (!aligned(t)) return refuse("tensor not 16-byte aligned");
+      rg = find_region(c, t, bytes, &off);
+      if (!rg || !rg->has_mc) return refuse("tensor is not in multicast-bound symmetric memory");
+      sym_tensor(c, rg, off, &in);
+      out = in;
+      break;
+    }
+    default: {  // all_gather: every list[j] symmetric; list[me] is where my shard lands
+      if (!aligned(op.in)) return refuse("input not 16-byte aligned");
+      for (int j = 0; j < n; ++j) {
+        size_t o = 0;
+        Region* r = find_region(c, op.list[j], bytes, &o);
+        if (!r || !r->has_mc || !aligned(op.list[j])) return refuse("an output tensor is not symmetric");
+        if (j == me) {
+          rg = r;
+          off = o;
+        }
+      }
+      sym_tensor(c, rg, off, &out);
+      in.local = const_cast<char*>(static_cast<const char*>(op.in));
+      break;
+    }
+  }
+  // tiny messages stay on the flag-in-data kernels (two barriers cost more than they do)
+  if (!forced && bytes <= sym_min_bytes(n)) return PDCC_OK;
+  *taken = 1;
+  return launch_sym(c->dev, ring_limit(c), op, in, out, stream);
+}
+
 int pdcc_collective(pdcc_comm_t* c, const pdcc_op_t* op_in, void* stream) {
   if (!c || !op_in) return PDCC_EINVAL;
   pdcc_op_t op = *op_in;
@@ -879,6 +1107,13 @@ int pdcc_collective(pdcc_comm_t* c, const pdcc_op_t* op_in, void* stream) {
   if (op.count == 0 && op.coll != PDCC_BARRIER) return PDCC_OK;
   int rc = validate_ptrs(op, c->cfg.rank, c->cfg.nranks);
   if (rc) return rc;
+  int taken = 0;
+  rc = try_symmetric(c, op, stream, &taken);
+  if (rc || taken) return rc;
+  if (op.algo == PDCC_ALGO_SYM) {
+    set_error("zero-copy path requested but the tensors are not symmetric memory of this communicator");
+    return PDCC_EINVAL;
+  }
   Plan p;
   rc = plan_collective(c->dev, ring_limit(c), c->has_mc, op, &p);
   if (rc) return rc;

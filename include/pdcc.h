@@ -136,6 +136,11 @@ typedef struct {
 int pdcc_comm_create(pdcc_store_t* store, const pdcc_comm_config_t* cfg, pdcc_comm_t** out);
 int pdcc_comm_destroy(pdcc_comm_t* comm);
 int pdcc_comm_info(pdcc_comm_t* comm, pdcc_comm_info_t* info);
+/* Tracing: with PDCC_TRACE=1 in the environment CTA 0 of every pipeline
+ * kernel records a timeline of its stages (admission waits, tile work, publisher fences)
+ * into the block; this copies it out (8 uint32 per event, layout in csrc/common.h) and
+ * clears it. Synchronises the device. */
+int pdcc_comm_read_trace(pdcc_comm_t* comm, uint32_t* out, int cap_events, int* count);
 /* Synchronises the device and returns PDCC_EPEER if any kernel of this comm
  * hit a device-side wait timeout since the last check (details in last_error). */
 int pdcc_comm_check(pdcc_comm_t* comm);
@@ -174,7 +179,9 @@ enum pdcc_algo {
   PDCC_ALGO_P2P = 5,          /* rooted / gather-type collectives: posted peer stores (push)  */
   PDCC_ALGO_NVLS = 6,         /* rooted / gather-type collectives: multicast                  */
   PDCC_ALGO_LL = 7,           /* any collective, small messages: flag-in-data push, no fences */
-  PDCC_ALGO_PULL = 8          /* all_gather: stage own shard, read every peer's (remote loads)  */
+  PDCC_ALGO_PULL = 8,         /* all_gather: stage own shard, read every peer's (remote loads)  */
+  PDCC_ALGO_SYM = 9           /* zero-copy on symmetric memory (pdcc_sym_alloc): multimem ops
+                                 straight on the user's tensor, two barriers per call          */
 };
 
 typedef struct {
@@ -193,6 +200,23 @@ typedef struct {
   void* list[PDCC_MAX_RANKS]; /* scatter: inputs on root; gather/all_gather:
                                  outputs. One pointer per group rank.         */
 } pdcc_op_t;
+
+/* ------------------------------------------------------------------------ *
+ * Symmetric memory. pdcc_sym_alloc is COLLECTIVE over
+ * the communicator: every rank calls it with the same size in the same order
+ * and gets memory that every rank has mapped and that is bound to a multicast
+ * object of its own. A tensor placed there (same offset on every rank) takes
+ * the zero-copy kernels: all_reduce / reduce / broadcast / all_gather work on
+ * it directly with multimem instructions, no staging and no tile flags.
+ * Contract: in one call either every rank passes symmetric tensors of the same
+ * allocation and offset, or none does. AUTO picks the zero-copy kernels for
+ * symmetric tensors above the small-message threshold; PDCC_ALGO_SYM forces
+ * them (error if not applicable). Regions are released by pdcc_comm_destroy.
+ * No counterpart in the reference; role of ncclMemAlloc + ncclCommRegister.
+ * ------------------------------------------------------------------------ */
+int pdcc_sym_alloc(pdcc_comm_t* comm, size_t bytes, void** ptr);
+int pdcc_sym_query(pdcc_comm_t* comm, const void* ptr, size_t bytes, int* is_symmetric,
+                   int* has_multicast);
 
 /* Generic launcher: validates, picks algo/grid, enqueues one kernel. */
 int pdcc_collective(pdcc_comm_t* comm, const pdcc_op_t* op, void* stream);
@@ -256,16 +280,23 @@ int pdcc_emu_check(pdcc_emu_t* emu);
  * static __device__ array of about 44 MiB that every GPU loading the library
  * holds until exit. In-place SUM/PRODUCT/MIN/MAX over buf0 and buf1 (count
  * elements each, both on `device`); afterwards both hold the result.
- *   - count * sizeof(dtype) must not exceed PDCC_NOALLOC_MAX_BYTES.
+ *   - count * sizeof(dtype) must not exceed PDCC_NOALLOC_MAX_BYTES; dtypes
+ *     without a reduction kernel and tensors that are not on `device` are
+ *     refused before anything is enqueued.
  *   - The first call on a device resolves the array's device address and zeroes
  *     its flags; it synchronises, so make it before any stream capture.
  *   - All calls on a device share the array: run them on one stream; calls
  *     that overlap on the GPU race.
- *   - Calls no cudaMalloc / cudaFree / allocating routine.
+ *   - Calls no cudaMalloc / cudaFree / allocating routine, reads no host memory
+ *     from the stream, and leaves the caller's current device as it was.
+ * pdcc_emu2_noalloc_check(device) waits for the device and returns PDCC_EPEER
+ * if a device-side wait timed out in any no-alloc call since the last check
+ * (the record is kept until it is read here); it allocates nothing either.
  * ------------------------------------------------------------------------ */
 #define PDCC_NOALLOC_MAX_BYTES (64ull << 20)
 int pdcc_emu2_all_reduce_noalloc(int device, void* buf0, void* buf1, uint64_t count, int dtype,
                                  int redop, void* stream);
+int pdcc_emu2_noalloc_check(int device);
 
 /* ------------------------------------------------------------------------ *
  * K9  Local helpers used by the world-size-1 degenerate paths and by the

@@ -127,6 +127,7 @@ def lib() -> C.CDLL:
         "pdcc_comm_destroy": [vp],
         "pdcc_comm_info": [vp, C.POINTER(CommInfo)],
         "pdcc_comm_check": [vp],
+        "pdcc_comm_read_trace": [vp, C.POINTER(C.c_uint32), ci, C.POINTER(ci)],
         "pdcc_collective": [vp, C.POINTER(Op), vp],
         "pdcc_plan": [vp, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci),
                       C.POINTER(C.c_uint64), C.POINTER(ci), C.POINTER(ci), C.POINTER(C.c_uint32)],
@@ -148,6 +149,7 @@ def lib() -> C.CDLL:
         "pdcc_all_gather": [vp, C.POINTER(vp), vp, C.c_uint64, ci, vp],
         "pdcc_barrier": [vp, vp],
         "pdcc_emu2_all_reduce_noalloc": [ci, vp, vp, C.c_uint64, ci, ci, vp],
+        "pdcc_emu2_noalloc_check": [ci],
     }
     for name, argtypes in sigs.items():
         fn = getattr(L, name)

@@ -114,17 +114,37 @@ class NativeComm:
         self._dev = torch.device("cuda", self.device)
         self._collective = L.pdcc_collective
         self._launches = 0
+        # A communicator's rings and flag counters are one sequence: kernels of one comm must
+        # not overlap on the GPU. Calls on one stream are ordered by the stream; when the
+        # caller moves to another stream the new stream is made to wait for the old one.
+        self._last_stream: Optional[int] = None
+        self._order_event: Optional[torch.cuda.Event] = None
 
     # -- plumbing ---------------------------------------------------------------------
     def _run(self, op: N.Op, stream: Optional[torch.cuda.Stream]) -> None:
         if _NVTX:  # one NVTX range per collective, off unless PDCC_NVTX=1
             torch.cuda.nvtx.range_push(f"pdcc.{_COLL_NAMES[op.coll]}[{op.count}]")
-        rc = self._collective(self._h, self._op_ref if op is self._op else C.byref(op),
-                              _stream_ptr(stream, self.device))
+        sp = _stream_ptr(stream, self.device)
+        if sp != self._last_stream:
+            self._switch_stream(sp)
+        rc = self._collective(self._h, self._op_ref if op is self._op else C.byref(op), sp)
         if _NVTX:
             torch.cuda.nvtx.range_pop()
         if rc != 0:
             N.check(rc)
+
+    def _switch_stream(self, sp: int) -> None:
+        """Orders the next kernel (on raw stream `sp`) after everything this communicator
+        has enqueued on the stream it used last. One event record + one stream wait, only
+        when the stream actually changes; never a host synchronisation."""
+        if self._last_stream is not None and not torch.cuda.is_current_stream_capturing():
+            if self._order_event is None:
+                self._order_event = torch.cuda.Event()
+            old = torch.cuda.ExternalStream(self._last_stream, device=self._dev)
+            new = torch.cuda.ExternalStream(sp, device=self._dev)
+            self._order_event.record(old)
+            new.wait_event(self._order_event)
+        self._last_stream = sp
 
     def plan(self, coll: int, count: int, dtype: torch.dtype, *, redop: int = SUM, algo=None,
              nblocks: int = 0) -> dict:
@@ -142,6 +162,23 @@ class NativeComm:
     def check(self) -> None:
         """Synchronises and raises if a device-side wait timed out in any kernel so far."""
         N.check(N.lib().pdcc_comm_check(self._h))
+
+    def read_trace(self, cap: int = 2048) -> list:
+        """Timeline CTA 0 recorded since the last read (PDCC_TRACE=1): a list of dicts
+        {kind, stage, warp, tile, begin_ns, end_ns, aux}. Synchronises the device."""
+        buf = (C.c_uint32 * (8 * cap))()
+        n = C.c_int()
+        N.check(N.lib().pdcc_comm_read_trace(self._h, buf, cap, C.byref(n)))
+        out = []
+        for i in range(min(n.value, cap)):
+            e = buf[8 * i:8 * i + 8]
+            kind = e[0] & 0xff
+            out.append({"kind": "worker" if kind < 16 else "fence" if kind == 16 else "admit",
+                        "stage": kind if kind < 16 else (kind - 32 if kind >= 32 else -1),
+                        "warp": (e[0] >> 8) & 0xff, "tile": e[1],
+                        "begin_ns": e[2] | (e[3] << 32), "end_ns": e[4] | (e[5] << 32),
+                        "aux": e[6]})
+        return out
 
     def destroy(self) -> None:
         if self._h:

@@ -303,7 +303,8 @@ def dp_mlp_check(rank, size):
     dev = demos.device()
     dtype = torch.float32
     torch.manual_seed(1234 + rank)  # ranks start with DIFFERENT params: broadcast must fix it
-    model = MLP(hidden=32, layers=3, dtype=dtype, device=dev)
+    # initialise on the CPU generator (the oracle below does the same), then move
+    model = MLP(hidden=32, layers=3, dtype=dtype).to(dev)
     tr = DataParallelTrainer(model, lr=0.1, bucket_bytes=3000)  # several buckets
     g = torch.Generator(device="cpu").manual_seed(7)
     xs = torch.randn(size, 8, 32, generator=g)

@@ -24,10 +24,19 @@ from pdcc_b200.ops import collectives as K
 pytestmark = pytest.mark.gpu
 
 
-def _no_alloc(bufs, redop=K.SUM):
+def _check():
+    """Waits for the device; raises if a wait inside a no-alloc kernel ran out of time."""
+    rc = N.lib().pdcc_emu2_noalloc_check(0)
+    if rc != 0:
+        raise N.PdccError(rc, N.lib().pdcc_last_error().decode())
+
+
+def _no_alloc(bufs, redop=K.SUM, dtype_code=None):
     fn = N.lib().pdcc_emu2_all_reduce_noalloc
+    if dtype_code is None:
+        dtype_code = K.dtype_code(bufs[0].dtype, True)
     rc = fn(0, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[0].numel(),
-            K.dtype_code(bufs[0].dtype, True), redop, torch.cuda.current_stream().cuda_stream)
+            dtype_code, redop, torch.cuda.current_stream().cuda_stream)
     if rc != 0:
         raise N.PdccError(rc, N.lib().pdcc_last_error().decode())
 
@@ -47,7 +56,7 @@ def test_matches_allocating_entry_point_twice(dtype, count):
             emu.check()
             got = [s.clone() for s in src]
             _no_alloc(got)
-            torch.cuda.synchronize()
+            _check()
             for r in range(2):
                 torch.testing.assert_close(got[r].float(), want[r].float(), rtol=tol, atol=tol)
             assert torch.equal(got[0], got[1]), "both ranks must hold the identical result"
@@ -61,7 +70,7 @@ def test_other_ops_and_second_use_of_the_scratch():
         b = torch.randn(70001, device="cuda")
         want = ref(a, b)
         _no_alloc([a, b], redop)
-        torch.cuda.synchronize()
+        _check()
         torch.testing.assert_close(a, want, rtol=1e-6, atol=1e-6)
         assert torch.equal(a, b)
 
@@ -79,5 +88,20 @@ def test_rejects_sizes_beyond_the_stated_maximum():
     a = torch.ones(limit // 4, device="cuda")
     b = torch.ones_like(a)
     _no_alloc([a, b])
-    torch.cuda.synchronize()
+    _check()
     assert float(a[0]) == 2.0 and float(b[-1]) == 2.0
+
+
+def test_refuses_bad_arguments_before_enqueuing_and_keeps_the_current_device():
+    a = torch.ones(16, dtype=torch.int8, device="cuda")  # int8 has no reduction kernel
+    with pytest.raises(N.PdccError) as e:
+        _no_alloc([a, a.clone()], dtype_code=N.I8)
+    assert e.value.code == N.EUNSUPPORTED
+    host = torch.ones(16).pin_memory()                   # not device memory of device 0
+    dev = torch.ones(16, device="cuda")
+    with pytest.raises(N.PdccError) as e:
+        _no_alloc([dev, host])
+    assert e.value.code == N.EINVAL and "not device memory" in str(e.value)
+    assert float(dev[0]) == 1.0
+    assert torch.cuda.current_device() == 0
+    _check()
