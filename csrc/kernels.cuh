@@ -31,7 +31,7 @@
 namespace pdcc {
 
 constexpr int kThreads = 512;     // LL kernels: one 16-byte unit per thread
-constexpr int kMaxThreads = 512;  // pipeline kernels: 16 warps shared by the stage groups (128 regs each)
+constexpr int kMaxThreads = 512;   // pipeline kernels: 2 control warps + 14 worker warps (128 registers each)
 
 struct KArgs {
   RankArgs r;           // this rank's view (real multi-GPU launch)
@@ -946,20 +946,20 @@ struct MovePolicy {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j) {
         const char* src = static_cast<const char*>(c.a->list[j]) + off;
-        if (j == c.rank) copy_bytes<LD_USER, 4>(c, static_cast<char*>(c.a->out) + off, src, len);
+        if (j == c.rank) copy_bytes<LD_USER, 8>(c, static_cast<char*>(c.a->out) + off, src, len);
         else push<false>(src, len, so, so, 1u << j);
       }
     } else if constexpr (KIND == MV_GATHER) {
       const char* src = static_cast<const char*>(c.a->in) + off;
       if (c.rank == k.root) {
-        copy_bytes<LD_USER, 4>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
+        copy_bytes<LD_USER, 8>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
       } else {
         push<false>(src, len, so + size_t(c.rank) * k.stride, so, 1u << k.root);
       }
     } else if constexpr (KIND == MV_ALLGATHER_PULL) {
       const char* src = static_cast<const char*>(c.a->in) + off;
-      copy_bytes<LD_USER, 4>(c, c.mine(so), src, len);
-      copy_bytes<LD_USER, 4>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
+      copy_bytes<LD_USER, 8>(c, c.mine(so), src, len);
+      copy_bytes<LD_USER, 8>(c, static_cast<char*>(c.a->list[c.rank]) + off, src, len);
     } else if constexpr (KIND == MV_ALLGATHER_NVLS) {
       const char* src = static_cast<const char*>(c.a->in) + off;
       const size_t sub = so + size_t(c.rank) * k.stride;
@@ -996,7 +996,7 @@ struct MovePolicy {
       if (c.rank != k.root) return;
       for (int j = 0; j < c.n; ++j)
         if (j != c.rank)
-          copy_bytes<LD_SYS, 4>(c, static_cast<char*>(c.a->list[j]) + off,
+          copy_bytes<LD_SYS, 8>(c, static_cast<char*>(c.a->list[j]) + off,
                                 c.mine(so + size_t(j) * k.stride), len);
     } else if constexpr (KIND == MV_ALLGATHER_PULL) {
       for (int i = 1; i < c.n; ++i) {

@@ -95,7 +95,7 @@ static int env_int(const char* name, int dflt) {
 struct PlanEnv {
   int ll_max;             // PDCC_LL_MAX            bytes; <0 = default (512 KiB / n)
   int oneshot_p2p_max;    // PDCC_ONESHOT_P2P_MAX   all_reduce one-shot up to this size (n > 2)
-  int nvls_min_ranks;     // PDCC_NVLS_MIN_RANKS    all_reduce uses the switch above this group size
+  int nvls_min_ranks;     // PDCC_NVLS_MIN_RANKS    all_reduce / reduce use the switch above this group size
   int rooted_twoshot_min; // PDCC_ROOTED_TWOSHOT_MIN reduce/broadcast: two-phase from this size
   int max_ctas;           // PDCC_MAX_CTAS          hard cap on CTAs per call (0 = none)
   int default_ctas;       // PDCC_DEFAULT_CTAS      cap below 8 MiB (0 = 128; >0 also caps big ones)
@@ -111,7 +111,7 @@ static std::atomic<int> g_plan_env_state{0};  // 0 = not read, 1 = valid
 static void read_plan_env(PlanEnv* e) {
   e->ll_max = env_int("PDCC_LL_MAX", -1);
   e->oneshot_p2p_max = env_int("PDCC_ONESHOT_P2P_MAX", 1 << 20);
-  e->nvls_min_ranks = env_int("PDCC_NVLS_MIN_RANKS", 4);
+  e->nvls_min_ranks = env_int("PDCC_NVLS_MIN_RANKS", 3);
   e->rooted_twoshot_min = env_int("PDCC_ROOTED_TWOSHOT_MIN", 2 << 20);
   e->max_ctas = env_int("PDCC_MAX_CTAS", 0);
   e->default_ctas = env_int("PDCC_DEFAULT_CTAS", 0);
@@ -137,8 +137,11 @@ static const PlanEnv& plan_env() {
 // Payload bytes per CTA per tile when the caller does not force one (PDCC_TILE_BYTES).
 // Measured table (profiles/): see DESIGN.md §4 "tiles".
 static uint64_t default_tile(int coll, int algo, int n, uint64_t bytes) {
+  // 64 KiB per CTA per tile: with 148 CTAs a 256 MiB message is 28 tiles per CTA, the
+  // pipeline fill is a few percent, and 16 slots of it fit the default 1 MiB ring for the
+  // NVLS and mover layouts (profiles/sweep_r2_*.jsonl: 32-64 KiB best at 4 and 8 GPUs,
+  // 128 KiB and more lose 5-15 %).
   (void)coll; (void)algo; (void)n;
-  if (bytes >= (uint64_t(64) << 20)) return 128 << 10;
   if (bytes >= (uint64_t(8) << 20)) return 64 << 10;
   return 32 << 10;
 }
@@ -231,7 +234,11 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
       // link rate (profiles/). Large messages: two-shot push where only the non-root ranks
       // own chunks: S bytes in and out of every GPU, all of it posted stores.
       const uint64_t big = uint64_t(plan_env().rooted_twoshot_min);
-      if (n > 2 && bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
+      // Large: every rank multimem.ld_reduce's 1/n of each tile and hands it to the root
+      // (measured 4 GPUs 256 MiB: 560 us against 617 us for the push variant and 433 us for
+      // NCCL; 8 GPUs: 595 against 684). Without the switch: the push variant.
+      if (n > 2 && bytes >= big) algo = (nvls && n > plan_env().nvls_min_ranks) ? PDCC_ALGO_TWOSHOT_NVLS
+                                                                               : PDCC_ALGO_TWOSHOT_P2P;
       else if (nvls && n >= 4) algo = PDCC_ALGO_NVLS;
       else algo = PDCC_ALGO_P2P;
     }
@@ -256,8 +263,7 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
         // themselves (two-phase, unicast stores, S bytes per GPU and direction).
         const uint64_t big = uint64_t(plan_env().rooted_twoshot_min);
         if (n <= 2) algo = PDCC_ALGO_P2P;
-        else if (mc_ok && n <= 4) algo = PDCC_ALGO_NVLS;  // measured: replication to <= 3 peers keeps up
-        else if (bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;
+        else if (bytes >= big) algo = PDCC_ALGO_TWOSHOT_P2P;  // 4 GPUs 256 MiB: 477-494 us, NVLS 511
         else algo = mc_ok ? PDCC_ALGO_NVLS : PDCC_ALGO_P2P;
       } else {
         // Posted stores beat remote loads on NVLink (profiles/): push my shard into every

@@ -14,7 +14,7 @@ from .distributed import (  # noqa: F401
     Group, GroupMember, ReduceOp, Work, all_gather, all_reduce, all_reduce_avg, barrier,
     broadcast, destroy_process_group, gather, get_backend, get_global_rank, get_group_rank,
     get_rank, get_world_size, init_process_group, is_initialized, native_comm, new_group, reduce,
-    scatter,
+    scatter, empty_symmetric, is_symmetric,
 )
 from .launcher import find_free_port, init_process, launch  # noqa: F401
 

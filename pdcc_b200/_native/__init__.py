@@ -24,11 +24,11 @@ ALL_REDUCE, REDUCE, BROADCAST, SCATTER, GATHER, ALL_GATHER, BARRIER = range(7)
 F32, BF16, F16, F64, I32, I64, U8, I8, I16 = range(9)
 # enum pdcc_algo
 (ALGO_AUTO, ALGO_ONESHOT_P2P, ALGO_TWOSHOT_P2P, ALGO_ONESHOT_NVLS, ALGO_TWOSHOT_NVLS, ALGO_P2P,
- ALGO_NVLS, ALGO_LL, ALGO_PULL) = range(9)
+ ALGO_NVLS, ALGO_LL, ALGO_PULL, ALGO_SYM) = range(10)
 ALGO_NAMES = {
     "auto": ALGO_AUTO, "oneshot_p2p": ALGO_ONESHOT_P2P, "twoshot_p2p": ALGO_TWOSHOT_P2P,
     "oneshot_nvls": ALGO_ONESHOT_NVLS, "twoshot_nvls": ALGO_TWOSHOT_NVLS,
-    "p2p": ALGO_P2P, "nvls": ALGO_NVLS, "ll": ALGO_LL, "pull": ALGO_PULL,
+    "p2p": ALGO_P2P, "nvls": ALGO_NVLS, "ll": ALGO_LL, "pull": ALGO_PULL, "sym": ALGO_SYM,
 }
 HANDLE_AUTO, HANDLE_POSIX_FD, HANDLE_LEGACY_IPC, HANDLE_LOCAL = range(4)
 HANDLE_NAMES = {HANDLE_AUTO: "auto", HANDLE_POSIX_FD: "posix_fd", HANDLE_LEGACY_IPC: "legacy_ipc",
@@ -129,6 +129,8 @@ def lib() -> C.CDLL:
         "pdcc_comm_check": [vp],
         "pdcc_comm_read_trace": [vp, C.POINTER(C.c_uint32), ci, C.POINTER(ci)],
         "pdcc_collective": [vp, C.POINTER(Op), vp],
+        "pdcc_sym_alloc": [vp, C.c_size_t, C.POINTER(vp)],
+        "pdcc_sym_query": [vp, vp, C.c_size_t, C.POINTER(ci), C.POINTER(ci)],
         "pdcc_plan": [vp, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci), C.POINTER(ci),
                       C.POINTER(C.c_uint64), C.POINTER(ci), C.POINTER(ci), C.POINTER(C.c_uint32)],
         "pdcc_plan_dry": [ci, ci, C.c_size_t, ci, C.POINTER(Op), C.POINTER(ci), C.POINTER(ci),

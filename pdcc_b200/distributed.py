@@ -38,7 +38,7 @@ __all__ = [
     "ReduceOp", "GroupMember", "Group", "Work", "init_process_group", "destroy_process_group",
     "is_initialized", "new_group", "get_rank", "get_world_size", "get_backend", "get_group_rank",
     "get_global_rank", "reduce", "all_reduce", "all_reduce_avg", "scatter", "gather", "all_gather",
-    "broadcast", "barrier", "native_comm",
+    "broadcast", "barrier", "native_comm", "empty_symmetric", "is_symmetric",
 ]
 
 NATIVE_BACKENDS = ("b200", "native", "nvlink")
@@ -366,6 +366,36 @@ def native_comm(group: Optional[Group] = None) -> K.NativeComm:
             multicast=-1 if mc is None else int(mc), handle_kind=kind,
             device_timeout_ms=int(os.environ.get("PDCC_DEVICE_TIMEOUT_MS", "0")))
     return g.comm
+
+
+def empty_symmetric(*shape, dtype: torch.dtype = torch.float32, group=None) -> torch.Tensor:
+    """A CUDA tensor in the group's symmetric memory. COLLECTIVE: every member of the group
+    calls it with the same shape and dtype, in the same order (like `new_group`).
+
+    Collectives on such tensors skip every staging copy: all_reduce / reduce / broadcast /
+    all_gather run as multimem instructions straight on the tensor (`csrc/sym.cuh`), which is
+    what gradient buckets and other long-lived communication buffers should live in. The
+    contract is NCCL's registered-buffer contract: in one call either every rank passes
+    tensors of the same symmetric allocation (same offset), or none does. On a group of one,
+    or without NVSwitch multicast, an ordinary tensor is returned (nothing to gain).
+    No counterpart in the reference (its tensors are 4-byte CPU tensors, main.py:12)."""
+    if len(shape) == 1 and isinstance(shape[0], (tuple, list, torch.Size)):
+        shape = tuple(shape[0])
+    g = _resolve(group)
+    if g is None:
+        raise ValueError("this rank is not a member of the group")
+    if g.size() == 1 or _S.backend != "b200":
+        dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else "cpu"
+        return torch.empty(*shape, dtype=dtype, device=dev)
+    comm = native_comm(g)
+    if not comm.has_multicast:
+        return torch.empty(*shape, dtype=dtype, device=torch.device("cuda", comm.device))
+    return comm.empty_symmetric(shape, dtype)
+
+
+def is_symmetric(tensor: torch.Tensor, group=None) -> bool:
+    g = _resolve(group)
+    return bool(g is not None and g.comm is not None and tensor.is_cuda and g.comm.is_symmetric(tensor))
 
 
 def _finish(async_op: bool, cuda: bool, torch_work=None) -> Optional[Work]:

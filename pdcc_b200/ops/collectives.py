@@ -82,6 +82,16 @@ def _fill(op: N.Op, coll: int, count: int, dtype: int, *, out_dtype: Optional[in
     return op
 
 
+class _RawCudaBytes:
+    """`n` bytes of device memory at `ptr`, exposed through __cuda_array_interface__ so that
+    torch can alias it without copying. `keep` pins whatever owns the memory."""
+
+    def __init__(self, ptr: int, n: int, keep):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "|u1", "data": (ptr, False),
+                                         "version": 2}
+        self._keep = keep
+
+
 class NativeComm:
     """One rank's communicator for one group (C type pdcc_comm_t)."""
 
@@ -132,6 +142,43 @@ class NativeComm:
             torch.cuda.nvtx.range_pop()
         if rc != 0:
             N.check(rc)
+
+    # -- symmetric memory ---------------------------------------------------------------
+    def empty_symmetric(self, shape, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+        """COLLECTIVE: every rank of the group calls it with the same shape and dtype, in the
+        same order. Returns a tensor in symmetric memory (same offset of the same region on
+        every rank, mapped on every rank, bound to a multicast object): collectives on it
+        take the zero-copy kernels (csrc/sym.cuh). Memory is carved from regions of
+        PDCC_SYM_CHUNK bytes (default 256 MiB; larger requests get a region of their own) and
+        lives until the communicator is destroyed."""
+        if isinstance(shape, int):
+            shape = (shape,)
+        numel = 1
+        for d in shape:
+            numel *= int(d)
+        if numel == 0:
+            return torch.empty(*shape, dtype=dtype, device=self._dev)
+        esz = torch.empty(0, dtype=dtype).element_size()
+        nbytes = numel * esz
+        need = (nbytes + 255) // 256 * 256
+        if not hasattr(self, "_sym_base") or self._sym_left < need:
+            chunk = max(need, int(os.environ.get("PDCC_SYM_CHUNK", str(256 << 20))))
+            ptr = C.c_void_p()
+            N.check(N.lib().pdcc_sym_alloc(self._h, chunk, C.byref(ptr)))
+            self._sym_base, self._sym_left = int(ptr.value), chunk
+        ptr_i = self._sym_base
+        self._sym_base += need
+        self._sym_left -= need
+        raw = torch.as_tensor(_RawCudaBytes(ptr_i, nbytes, self), device=self._dev)
+        if raw.data_ptr() != ptr_i:
+            raise RuntimeError("torch copied the symmetric buffer instead of aliasing it")
+        return raw.view(dtype)[:numel].view(*shape)
+
+    def is_symmetric(self, t: torch.Tensor) -> bool:
+        s, m = C.c_int(), C.c_int()
+        N.check(N.lib().pdcc_sym_query(self._h, t.data_ptr(), t.numel() * t.element_size(),
+                                       C.byref(s), C.byref(m)))
+        return bool(s.value)
 
     def _switch_stream(self, sp: int) -> None:
         """Orders the next kernel (on raw stream `sp`) after everything this communicator

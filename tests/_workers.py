@@ -296,6 +296,120 @@ def native_sweep(rank, size):
                           "multicast": comm.has_multicast, "handle": comm.handle_kind})
 
 
+def symmetric_checks(rank, size):
+    """Zero-copy collectives on tensors from dist.empty_symmetric (csrc/sym.cuh) against the
+    same oracle as native_sweep, AUTO routing and forced, interleaved with staged calls."""
+    from pdcc_b200.ops import collectives as K
+
+    torch.set_num_threads(4)
+    dev = demos.device()
+    world = dist.new_group(list(range(size)))
+    comm = dist.native_comm(world)
+    res = {"multicast": comm.has_multicast, "failures": [], "checked": 0}
+    if not comm.has_multicast:
+        _save(rank, "sym", res)
+        return
+    fails = res["failures"]
+
+    def oracle(count, dtype, seed, op):
+        st = torch.stack([_det_input(r, count, dtype, seed, "cpu").double() for r in range(size)])
+        return {"SUM": st.sum(0), "MIN": st.min(0).values, "MAX": st.max(0).values}[op]
+
+    seed = 9000
+    sizes = [16, 16 * 1024 + 16, 300 * 1024, (2 << 20) + 64, (8 << 20) + 16 * size * 3]  # elements
+    for dtype, ops in ((torch.float32, ("SUM",)), (torch.bfloat16, ("SUM", "MAX", "MIN"))):
+        k = 16 // torch.empty(0, dtype=dtype).element_size()
+        for opname in ops:
+            op = {"SUM": K.SUM, "MIN": K.MIN, "MAX": K.MAX}[opname]
+            for count in sizes:
+                count = count // k * k  # the zero-copy kernels work on whole 16-byte units
+                for algo in (None, "sym"):
+                    seed += 1
+                    x = dist.empty_symmetric(count, dtype=dtype, group=world)
+                    assert dist.is_symmetric(x, world)
+                    x.copy_(_det_input(rank, count, dtype, seed, dev))
+                    comm.all_reduce(x, op, algo=algo)
+                    want = oracle(count, dtype, seed, opname)
+                    tol = 0.0 if opname != "SUM" else {torch.float32: 1e-5, torch.bfloat16: 4e-2}[dtype]
+                    res["checked"] += 1
+                    if not torch.allclose(x.cpu().double(), want, rtol=tol, atol=tol):
+                        fails.append(("all_reduce", str(dtype), opname, count, algo))
+    # fused average, reduce to both ends, broadcast (direct and two-phase), all_gather
+    for count in (4096, (4 << 20) + 16):
+        seed += 1
+        x = dist.empty_symmetric(count, group=world)
+        x.copy_(_det_input(rank, count, torch.float32, seed, dev))
+        dist.all_reduce_avg(x, group=world)
+        res["checked"] += 1
+        if not torch.allclose(x.cpu().double(), oracle(count, torch.float32, seed, "SUM") / size,
+                              rtol=1e-5, atol=1e-5):
+            fails.append(("avg", count))
+        for root in (0, size - 1):
+            seed += 1
+            x.copy_(_det_input(rank, count, torch.float32, seed, dev))
+            keep = x.clone()
+            comm.reduce(x, root, K.SUM, algo="sym")
+            res["checked"] += 1
+            if rank == root:
+                if not torch.allclose(x.cpu().double(), oracle(count, torch.float32, seed, "SUM"),
+                                      rtol=1e-5, atol=1e-5):
+                    fails.append(("reduce", count, root))
+            elif not torch.equal(x, keep):
+                fails.append(("reduce-nonroot-touched", count, root))
+            for algo in (None, "sym", "nvls"):
+                seed += 1
+                x.copy_(_det_input(rank, count, torch.float32, seed, dev))
+                comm.broadcast(x, root, algo=algo)
+                res["checked"] += 1
+                if not torch.equal(x.cpu(), _det_input(root, count, torch.float32, seed, "cpu")):
+                    fails.append(("broadcast", count, root, algo))
+        seed += 1
+        lst = [dist.empty_symmetric(count, dtype=torch.bfloat16, group=world) for _ in range(size)]
+        xin = _det_input(rank, count, torch.bfloat16, seed, dev)
+        for t in lst:
+            t.zero_()
+        comm.all_gather(lst, xin, algo="sym")
+        res["checked"] += 1
+        for p in range(size):
+            if not torch.equal(lst[p].cpu(), _det_input(p, count, torch.bfloat16, seed, "cpu")):
+                fails.append(("all_gather", count, p))
+                break
+    # interleave zero-copy and staged calls with no host sync in between
+    a = dist.empty_symmetric(1 << 20, group=world)
+    b = torch.empty(1 << 20, device=dev)
+    outs = []
+    for it in range(40):
+        t = a if it % 2 == 0 else b
+        t.fill_(float(rank + it))
+        comm.all_reduce(t, K.SUM)
+        outs.append((it, t[:4].clone(), t[-4:].clone()))
+    for it, h, tl in outs:
+        want = float(sum(r + it for r in range(size)))
+        res["checked"] += 1
+        if not (torch.all(h == want) and torch.all(tl == want)):
+            fails.append(("interleave", it, float(h[0]), want))
+    # graph capture of a zero-copy call
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            comm.all_reduce(a, K.SUM)
+    for i in range(1, 4):
+        a.fill_(float(rank + i))
+        graph.replay()
+        torch.cuda.synchronize()
+        res["checked"] += 1
+        want = float(sum(r + i for r in range(size)))
+        if float(a[0]) != want or float(a[-1]) != want:
+            fails.append(("graph", i, float(a[0]), want))
+    try:
+        comm.check()
+    except Exception as e:
+        fails.append(("device", str(e)))
+    _save(rank, "sym", res)
+
+
 def dp_mlp_check(rank, size):
     """D1: bucketed gradient averaging == one big-batch step (README.md:5), any backend."""
     from pdcc_b200.models.mlp import MLP, DataParallelTrainer

@@ -66,6 +66,19 @@ def test_sweep_correctness_native(tmp_path):
         assert res["checked"] > 50
 
 
+def test_symmetric_zero_copy_native(tmp_path):
+    """dist.empty_symmetric + the zero-copy kernels (multimem on the user's tensor)."""
+    n = _world()
+    dist.launch(_workers.symmetric_checks, size=n, backend="b200", timeout=600,
+                env={"PDCC_TEST_OUT": str(tmp_path)})
+    for r in range(n):
+        res = torch.load(os.path.join(tmp_path, f"sym_{r}.pt"))
+        if not res["multicast"]:
+            pytest.skip("no NVSwitch multicast on this box")
+        assert res["failures"] == [], res["failures"][:5]
+        assert res["checked"] > 60
+
+
 def test_data_parallel_native(tmp_path):
     """D1 on real GPUs: broadcast + bucketed fused all_reduce_avg overlapped with backward."""
     n = min(_world(), 4)
