@@ -61,6 +61,9 @@ def main() -> None:
     ap.add_argument("--env-sweep", default="",
                     help="A/B a planner knob inside ONE job, e.g. PDCC_TILE_SPLIT=0,1,4,8 "
                          "(the native planner reads its knobs from the environment per call)")
+    ap.add_argument("--symmetric", action="store_true",
+                    help="pdcc buffers come from dist.empty_symmetric (zero-copy kernels); the NCCL "
+                         "rows keep ordinary tensors")
     ap.add_argument("--graph", action="store_true",
                     help="also time small messages captured in a CUDA graph (device-only latency)")
     ap.add_argument("--graph-max", type=parse_size, default=1 << 20)
@@ -185,6 +188,11 @@ def main() -> None:
                 else torch.ones(count, dtype=dtype, device=dev)
             xs = x[:shard].clone()
             lst = [torch.empty(shard, dtype=dtype, device=dev) for _ in range(n)]
+            px, plst = x, lst  # what the pdcc rows use
+            if args.symmetric and member:
+                px = dist.empty_symmetric(count, dtype=dtype, group=group)
+                px.copy_(x)
+                plst = [dist.empty_symmetric(shard, dtype=dtype, group=group) for _ in range(n)]
             is_root = rank == root
 
             def make(impl, algo, nb):
@@ -201,12 +209,12 @@ def main() -> None:
                 a = None if algo == "auto" else algo
                 gr = group.to_group_rank(root)
                 return {
-                    "all_reduce": lambda: comm.all_reduce(x, kop, algo=a, nblocks=nb),
-                    "reduce": lambda: comm.reduce(x, gr, kop, algo=a, nblocks=nb),
-                    "broadcast": lambda: comm.broadcast(x, gr, algo=a, nblocks=nb),
+                    "all_reduce": lambda: comm.all_reduce(px, kop, algo=a, nblocks=nb),
+                    "reduce": lambda: comm.reduce(px, gr, kop, algo=a, nblocks=nb),
+                    "broadcast": lambda: comm.broadcast(px, gr, algo=a, nblocks=nb),
                     "scatter": lambda: comm.scatter(xs, lst if is_root else None, gr, algo=a, nblocks=nb),
                     "gather": lambda: comm.gather(xs, lst if is_root else None, gr, algo=a, nblocks=nb),
-                    "all_gather": lambda: comm.all_gather(lst, xs, algo=a, nblocks=nb),
+                    "all_gather": lambda: comm.all_gather(plst, xs, algo=a, nblocks=nb),
                 }[coll]
 
             for impl in impls:
@@ -252,6 +260,8 @@ def main() -> None:
                            "graph_us": graph_us}
                     if env_name is not None and impl == "pdcc":
                         row["env"] = {env_name: ev}
+                    if impl == "pdcc" and args.symmetric:
+                        row["symmetric"] = True
                     if impl == "pdcc":
                         row["plan"] = comm.plan(COLL_ID[coll],
                                                 count if coll in ("all_reduce", "reduce") else
@@ -267,7 +277,7 @@ def main() -> None:
                               f"alg {algbw:8.2f}  bus {row['busbw_GBps']:8.2f} GB/s  roof {row['roofline_frac']}"
                               + (f"  graph {graph_us} us" if graph_us is not None else ""),
                               flush=True)
-            del x, xs, lst
+            del x, xs, lst, px, plst
     if comm is not None:
         comm.check()
     dist.destroy_process_group()
