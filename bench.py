@@ -252,6 +252,35 @@ def run(D, rank: int, size: int, args, launch_count) -> dict:
         lat.append(timed(lambda: D.all_reduce(small, op=D.ReduceOp.SUM, group=suite.group), 200))
     small_p50 = statistics.median(lat) * 1e3
 
+    # ---- the same collectives on tensors from the library's symmetric memory (zero-copy
+    # kernels; explanatory, not part of `value`: the reference has no such allocator) -------
+    symmetric = None
+    if args.impl == "pdcc" and size > 1 and hasattr(D, "empty_symmetric"):
+        t_sym = D.empty_symmetric(suite.count, dtype=torch.float32, group=suite.group)
+        if D.is_symmetric(t_sym, suite.group):
+            t_sym.fill_(1e-20)
+            l_sym = [D.empty_symmetric(suite.shard, dtype=torch.float32, group=suite.group)
+                     for _ in range(size)]
+            calls = {
+                "reduce": lambda: D.reduce(t_sym, dst=0, op=D.ReduceOp.SUM, group=suite.group),
+                "all_reduce": lambda: D.all_reduce(t_sym, op=D.ReduceOp.SUM, group=suite.group),
+                "all_gather": lambda: D.all_gather(l_sym, suite.ag_in, group=suite.group),
+                "broadcast": lambda: D.broadcast(t_sym, src=0, group=suite.group),
+            }
+            symmetric = {}
+            for name, fn in calls.items():
+                fn()
+                ms = timed(fn, args.detail_iters)
+                algbw = suite.nbytes / (ms * 1e-3) / 1e9
+                symmetric[name] = {"ms": round(ms, 4), "algbw_GBps": round(algbw, 1),
+                                   "busbw_GBps": round(algbw * BUS_FACTOR[name](size), 1)}
+            # and one correctness check of the zero-copy all_reduce on the timed buffer
+            t_sym.copy_((torch.arange(suite.count, device=dev) % 251).to(torch.float32) + (rank + 1))
+            D.all_reduce(t_sym, op=D.ReduceOp.SUM, group=suite.group)
+            want = size * (torch.arange(suite.count, device=dev) % 251).to(torch.float32) + size * (size + 1) / 2.0
+            symmetric["all_reduce_verified"] = bool(torch.equal(t_sym, want))
+            del want
+
     # ---- verification: the timed call sites, on checkable inputs, on every rank ----------
     mine = suite.verify()
     bad = [k for k, v in mine.items() if not v]
@@ -304,6 +333,7 @@ def run(D, rank: int, size: int, args, launch_count) -> dict:
         },
         "per_collective": per, "small_msg_p50_us": round(small_p50, 2),
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "verified": verified,
+        "symmetric_memory": symmetric,
     }
 
 

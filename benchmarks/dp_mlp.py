@@ -5,10 +5,12 @@ by the fused all_reduce x 1/world kernel, bucket by bucket, overlapped with back
   torchrun --nproc-per-node 8 benchmarks/dp_mlp.py --steps 20
   python benchmarks/dp_mlp.py --gpus 2 --mode all
 
-Modes: `overlap` (side stream, default), `serial` (same kernels, no overlap), `nccl`
-(README.md:5 done the torch way: all_reduce(SUM) per gradient on NCCL, then divide).
-Reports ms/step (device-timed, max over ranks) and, for the pdcc modes, the exposed
-communication time = step time minus the step time of the same model with averaging off.
+Modes: `overlap` (side stream, buckets in symmetric memory: zero-copy fused average),
+`staged` (same, buckets in ordinary memory), `serial` (symmetric buckets, no overlap), `ddp`
+(torch.nn.parallel.DistributedDataParallel on NCCL: bucketed and overlapped, the real
+baseline) and `nccl` (README.md:5 done naively: all_reduce(SUM) per gradient on NCCL, then
+divide). Reports ms/step (device-timed, max over ranks) and the exposed communication
+time = step time minus the step time of the same model with averaging off.
 """
 from __future__ import annotations
 
@@ -29,7 +31,10 @@ def main() -> None:
     ap.add_argument("--hidden", type=int, default=8192)
     ap.add_argument("--layers", type=int, default=4)
     ap.add_argument("--batch", type=int, default=4096, help="per-GPU batch (weak scaling)")
-    ap.add_argument("--mode", default="all", choices=["overlap", "serial", "nccl", "all"])
+    ap.add_argument("--mode", default="all", choices=["overlap", "staged", "serial", "ddp", "nccl", "all"])
+    ap.add_argument("--comm-ctas", default="0", help="comma list: CTAs per averaging kernel in the "
+                    "overlap mode (0 = library default); more than one value adds overlap_c<N> rows")
+    ap.add_argument("--bucket-mb", type=int, default=128)
     args = ap.parse_args()
     if args.gpus > 1 and "RANK" not in os.environ:
         from pdcc_b200.launcher import find_free_port
@@ -73,7 +78,11 @@ def main() -> None:
         return float(t.item())
 
     results = {}
-    modes = ["overlap", "serial", "nccl"] if args.mode == "all" else [args.mode]
+    modes = ["overlap", "staged", "serial", "ddp", "nccl"] if args.mode == "all" else [args.mode]
+    from pdcc_b200.utils.clocks import ClockSampler
+
+    sampler = ClockSampler(torch.cuda.current_device())
+    sampler.__enter__()
     # compute-only reference: same model, averaging switched off
     torch.manual_seed(0)
     base = MLP(args.hidden, args.layers, device=dev)
@@ -86,7 +95,14 @@ def main() -> None:
 
     results["compute_only_ms"] = timed(compute_only)
     del base, opt
+    ctas_list = [int(v) for v in args.comm_ctas.split(",")]
+    expanded = []
     for mode in modes:
+        if mode == "overlap" and len(ctas_list) > 1:
+            expanded += [f"overlap_c{c}" for c in ctas_list]
+        else:
+            expanded.append(mode)
+    for mode in expanded:
         torch.manual_seed(0)
         model = MLP(args.hidden, args.layers, device=dev)
         if mode == "nccl":
@@ -100,13 +116,30 @@ def main() -> None:
                         tdist.all_reduce(p.grad, op=tdist.ReduceOp.SUM, group=nccl)
                         p.grad.div_(world)
                 opt.step()
+        elif mode == "ddp":
+            if nccl is None:
+                continue
+            from torch.nn.parallel import DistributedDataParallel as DDP
+
+            ddp = DDP(model, device_ids=[dev.index], process_group=nccl, bucket_cap_mb=128,
+                      gradient_as_bucket_view=True)
+            opt = torch.optim.SGD(ddp.parameters(), lr=1e-3)
+
+            def step():
+                opt.zero_grad(set_to_none=False)
+                torch.nn.functional.mse_loss(ddp(x).float(), y.float()).backward()
+                opt.step()
         else:
-            tr = DataParallelTrainer(model, overlap=(mode == "overlap"))
+            ctas = int(mode.split("_c")[1]) if "_c" in mode else ctas_list[0]
+            tr = DataParallelTrainer(model, overlap=(mode != "serial"), symmetric=(mode != "staged"),
+                                     comm_ctas=ctas, bucket_bytes=args.bucket_mb << 20)
 
             def step():
                 tr.step(x, y)
         results[mode + "_ms"] = timed(step)
         results[mode + "_exposed_comm_ms"] = results[mode + "_ms"] - results["compute_only_ms"]
+    sampler.__exit__(None, None, None)
+    results["clocks"] = sampler.summary()
     if rank == 0:
         grad_bytes = args.layers * (args.hidden * args.hidden + args.hidden) * 2
         print(json.dumps({"config": {"hidden": args.hidden, "layers": args.layers,

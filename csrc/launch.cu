@@ -339,11 +339,30 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   // stage group (a few microseconds, overlapped by the other groups) stays cheap.
   const uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
   uint64_t want = pe.tile_bytes > 0 ? uint64_t(pe.tile_bytes) : default_tile(op.coll, algo, n, bytes);
+  // mid-range messages: at least four tiles per CTA, so that the stages of one call overlap
+  // (one tile per CTA runs IN, MID, OUT back to back with a fence + flag hop between them)
+  if (pe.tile_bytes <= 0 && per_cta / 4 < want) want = per_cta / 4 > (8 << 10) ? per_cta / 4 : (8 << 10);
   uint64_t tile = per_cta < want ? per_cta : want;
   tile = round_up(tile, align);
+  // Depth before tile size: the publisher's fence delays every flag by 10-25 us, so a ring
+  // needs about eight tiles in flight to keep its IN stage busy (8 GPUs, gather with 64 KiB
+  // tiles and depth 2: 0.45 ms; round 1 with depth 4: 0.35 ms). Layouts that put n sub-slots
+  // in a slot (gather, all_gather, one-shot) therefore take smaller tiles instead of fewer.
   const int max_depth = pe.depth > 0 ? pe.depth : 16;
   int depth = 1;
   uint64_t slot = 0;
+  if (pe.tile_bytes <= 0) {
+    for (int want_depth = 8; want_depth >= 1; want_depth >>= 1) {
+      if (want_depth > max_depth) continue;
+      const uint64_t sl = (uint64_t(comm.ring_bytes) / uint64_t(want_depth)) & ~uint64_t(255);
+      const uint64_t cap = payload_cap(sl);
+      const uint64_t floor_tile = uint64_t(want_depth >= 4 ? (8 << 10) : 1);
+      if (cap >= tile || cap >= floor_tile || want_depth == 1) {
+        if (cap < tile) tile = cap;
+        break;
+      }
+    }
+  }
   for (int d = max_depth; d >= 1; d >>= 1) {
     const uint64_t sl = (uint64_t(comm.ring_bytes) / uint64_t(d)) & ~uint64_t(255);
     if (payload_cap(sl) >= tile || d == 1) {

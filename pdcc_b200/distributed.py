@@ -451,7 +451,8 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op: bool = False):
     return _gloo_wait(work, async_op)
 
 
-def all_reduce_avg(tensor, out=None, group=None, async_op: bool = False, scale=None):
+def all_reduce_avg(tensor, out=None, group=None, async_op: bool = False, scale=None,
+                   nblocks: int = 0):
     """K2 — the README's "send all gradients to all GPUs, average them" (README.md:5) as one
     kernel: sum over ranks, multiply by 1/world_size (or `scale`), optionally write fp32
     from a bf16/fp16 input. `out=None` averages in place."""
@@ -465,7 +466,9 @@ def all_reduce_avg(tensor, out=None, group=None, async_op: bool = False, scale=N
         if not tensor.numel():
             return _finish(async_op, True)
         if g.size() > 1:
-            native_comm(g).all_reduce(tensor, K.SUM, out=out, scale=s)
+            # nblocks caps the CTAs of the kernel: an average that overlaps a backward pass
+            # should leave most SMs to the GEMMs (parallel/data_parallel.py)
+            native_comm(g).all_reduce(tensor, K.SUM, out=out, scale=s, nblocks=nblocks)
         elif out is not None or s != 1.0:
             K.local_scale_cast(tensor if out is None else out, tensor, s)
         return _finish(async_op, True)

@@ -35,13 +35,15 @@ class DataParallelTrainer:
     each bucket's gradients exist), wait, local SGD step."""
 
     def __init__(self, model: nn.Module, lr: float = 1e-3, group=None, overlap: bool = True,
-                 bucket_bytes: int = 128 << 20, sync_params: bool = True):
+                 bucket_bytes: int = 128 << 20, sync_params: bool = True, symmetric: bool = True,
+                 comm_ctas: int = 0):
         self.model = model
         if sync_params and dist.is_initialized() and dist.get_world_size(group) > 1:
             broadcast_parameters(model, src=dist.get_global_rank(group, 0) if group else 0,
                                  group=group)
         self.avg = BucketedGradAverager(model.parameters(), group=group, overlap=overlap,
-                                        bucket_bytes=bucket_bytes)
+                                        bucket_bytes=bucket_bytes, symmetric=symmetric,
+                                        comm_ctas=comm_ctas)
         self.opt = torch.optim.SGD(model.parameters(), lr=lr)
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:

@@ -15,6 +15,7 @@ No host synchronisation anywhere: hooks only record/wait CUDA events.
 """
 from __future__ import annotations
 
+import os
 from typing import Iterable, List, Optional
 
 import torch
@@ -29,10 +30,23 @@ def broadcast_parameters(module: torch.nn.Module, src: int = 0, group=None) -> N
 
 
 class _Bucket:
-    def __init__(self, params: List[torch.nn.Parameter], dtype: torch.dtype, device):
+    def __init__(self, params: List[torch.nn.Parameter], dtype: torch.dtype, device, group=None,
+                 symmetric: bool = True):
         self.params = params
         self.numel = sum(p.numel() for p in params)
-        self.flat = torch.zeros(self.numel, dtype=dtype, device=device)
+        # Gradient buckets live in symmetric memory when the native backend is up: the fused
+        # average then runs as multimem.ld_reduce / multimem.st straight on the bucket
+        # (csrc/sym.cuh), no staging copy on either side. Padded to whole 16-byte units.
+        pad = 16 // torch.empty(0, dtype=dtype).element_size()
+        padded = (self.numel + pad - 1) // pad * pad
+        if (symmetric and device.type == "cuda" and dist.is_initialized()
+                and dist.get_backend() == "b200" and dist.get_world_size(group) > 1):
+            self.flat = dist.empty_symmetric(padded, dtype=dtype, group=group)
+            self.flat.zero_()
+            self.symmetric = dist.is_symmetric(self.flat, group)
+        else:
+            self.flat = torch.zeros(padded, dtype=dtype, device=device)
+            self.symmetric = False
         self.pending = len(params)
         self.ready = torch.cuda.Event() if device.type == "cuda" else None
         self.done = torch.cuda.Event() if device.type == "cuda" else None
@@ -51,12 +65,18 @@ class BucketedGradAverager:
     """
 
     def __init__(self, params: Iterable[torch.nn.Parameter], group=None,
-                 bucket_bytes: int = 128 << 20, overlap: bool = True):
+                 bucket_bytes: int = 128 << 20, overlap: bool = True, symmetric: bool = True,
+                 comm_ctas: int = 0):
         params = [p for p in params if p.requires_grad]
         if not params:
             raise ValueError("no trainable parameters")
         self.group = group
         self.overlap = overlap
+        # CTAs of each averaging kernel. The kernels keep one CTA per SM resident for their
+        # whole run; while backward is still producing gradients the GEMMs should keep most
+        # of the SMs, so overlapped averages run on a handful (measured on 4 GPUs: exposed communication 0.53 ms
+        # with 8 CTAs, 0.69 with 32, 1.27 with 148; DDP on NCCL 1.01).
+        self.comm_ctas = comm_ctas if comm_ctas > 0 else (int(os.environ.get("PDCC_DP_CTAS", "8")) if overlap else 0)
         self.device = params[0].device
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.buckets: List[_Bucket] = []
@@ -66,12 +86,12 @@ class BucketedGradAverager:
         for p in reversed(params):
             nbytes = p.numel() * p.element_size()
             if cur and (cur_bytes + nbytes > bucket_bytes or p.dtype != cur[0].dtype):
-                self.buckets.append(_Bucket(cur, cur[0].dtype, self.device))
+                self.buckets.append(_Bucket(cur, cur[0].dtype, self.device, group, symmetric))
                 cur, cur_bytes = [], 0
             cur.append(p)
             cur_bytes += nbytes
         if cur:
-            self.buckets.append(_Bucket(cur, cur[0].dtype, self.device))
+            self.buckets.append(_Bucket(cur, cur[0].dtype, self.device, group, symmetric))
         self._stream: Optional[torch.cuda.Stream] = None
         if self.device.type == "cuda" and overlap:
             self._stream = torch.cuda.Stream(device=self.device, priority=-1)
@@ -87,16 +107,21 @@ class BucketedGradAverager:
                 self._launch(b)
         return hook
 
+    def _ctas(self, b: _Bucket) -> int:
+        # the CTA cap is for the zero-copy kernels (the switch does the work, a handful of
+        # CTAs keep it fed); the staged kernels need their SMs (8 GPUs: 10.9 ms/step with 8)
+        return self.comm_ctas if b.symmetric else 0
+
     def _launch(self, b: _Bucket) -> None:
         if self.world == 1:
             return
         if self._stream is None:
-            dist.all_reduce_avg(b.flat, group=self.group)
+            dist.all_reduce_avg(b.flat, group=self.group, nblocks=self._ctas(b))
             return
         b.ready.record()  # on the compute stream: this bucket's gradients are complete
         self._stream.wait_event(b.ready)
         with torch.cuda.stream(self._stream):
-            dist.all_reduce_avg(b.flat, group=self.group)
+            dist.all_reduce_avg(b.flat, group=self.group, nblocks=self._ctas(b))
             b.done.record()
 
     def zero_grad(self) -> None:
