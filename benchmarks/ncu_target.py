@@ -1,7 +1,9 @@
-"""Small single-GPU program for `ncu --set full`: the K9 copy kernel of the 1-GPU bench, the
-world-size-1 all_reduce (tile pipeline with self-signalled flags) and one 4-rank emulated
-two-shot all_reduce (one cooperative kernel over all ranks' data, as B200_PROFILING.md asks
-for when there are fewer GPUs than ranks)."""
+"""Small single-GPU program for `ncu --set full` (B200_PROFILING.md: with fewer GPUs than ranks,
+emulate the ranks as ONE kernel over all ranks' data): four emulated ranks x 32 CTAs in one
+cooperative launch, the three pipeline kernels of the bench path that cross "links" (two-shot
+all_reduce, rooted two-shot reduce, two-phase broadcast), each launched twice so that
+`-k regex:'reduce_kernel|move_kernel' -s 3 -c 3` captures the warm second round, plus the K9
+local copy. Sizes are kept small: ncu saves and restores device memory around ~40 replays."""
 import os
 import sys
 
@@ -10,20 +12,17 @@ import torch
 from pdcc_b200.ops import collectives as K
 
 torch.cuda.set_device(0)
-n = 64 << 20
-src = torch.ones(n, device="cuda")
-dst = torch.empty_like(src)
-for _ in range(4):
-    K.local_copy(dst, src)
-comm = K.NativeComm(None, "ncu", 0, 1, 0)
-x = torch.ones(16 << 20, device="cuda")
-for _ in range(3):
-    comm.all_reduce(x, K.SUM, algo="twoshot_p2p")
-comm.check()
-emu = K.Emulator(4, 0, slot_bytes=1 << 20, max_blocks=32)
-xs = [torch.ones(8 << 20, device="cuda") for _ in range(4)]
-for _ in range(3):
+n = 4
+emu = K.Emulator(n, 0, slot_bytes=256 << 10, max_blocks=32)
+xs = [torch.full((4 << 20,), float(r + 1), device="cuda") for r in range(n)]  # 16 MiB each
+for _ in range(2):
     emu.all_reduce(xs, K.SUM, algo="twoshot_p2p")
+    emu.reduce(xs, 0, K.SUM, algo="twoshot_p2p")
+    emu.broadcast(xs, 0, algo="twoshot_p2p")
 emu.check()
+src = torch.ones(16 << 20, device="cuda")
+dst = torch.empty_like(src)
+for _ in range(2):
+    K.local_copy(dst, src)
 torch.cuda.synchronize()
-print("ok", float(dst[-1]), float(x[0]), float(xs[0][0]))
+print("ok", float(dst[-1]), float(xs[0][0]), float(xs[3][-1]))

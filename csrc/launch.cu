@@ -138,7 +138,7 @@ static const PlanEnv& plan_env() {
 // Measured table (profiles/): see DESIGN.md §4 "tiles".
 static uint64_t default_tile(int coll, int algo, int n, uint64_t bytes) {
   // 64 KiB per CTA per tile: with 148 CTAs a 256 MiB message is 28 tiles per CTA, the
-  // pipeline fill is a few percent, and 16 slots of it fit the default 1 MiB ring for the
+  // pipeline fill is a few percent, and 16 slots of it fit the default 2 MiB ring for the
   // NVLS and mover layouts (profiles/sweep_r2_*.jsonl: 32-64 KiB best at 4 and 8 GPUs,
   // 128 KiB and more lose 5-15 %).
   (void)coll; (void)algo; (void)n;
@@ -339,9 +339,6 @@ int plan_collective(const DevComm& comm, int ring_limit, bool has_mc, const pdcc
   // stage group (a few microseconds, overlapped by the other groups) stays cheap.
   const uint64_t per_cta = ceil_div(bytes ? bytes : 1, uint64_t(nb));
   uint64_t want = pe.tile_bytes > 0 ? uint64_t(pe.tile_bytes) : default_tile(op.coll, algo, n, bytes);
-  // mid-range messages: at least four tiles per CTA, so that the stages of one call overlap
-  // (one tile per CTA runs IN, MID, OUT back to back with a fence + flag hop between them)
-  if (pe.tile_bytes <= 0 && per_cta / 4 < want) want = per_cta / 4 > (8 << 10) ? per_cta / 4 : (8 << 10);
   uint64_t tile = per_cta < want ? per_cta : want;
   tile = round_up(tile, align);
   // Depth before tile size: the publisher's fence delays every flag by 10-25 us, so a ring

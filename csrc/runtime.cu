@@ -419,9 +419,11 @@ static int fill_dev(pdcc_comm* c) {
 
 static void sizes_from_cfg(pdcc_comm* c) {
   // One CTA's ring is PDCC_RING_DEPTH x slot_bytes; every call cuts it into slots of its own
-  // size (plan_collective). 1 MiB per ring by default: 148 rings + header = 166 MiB per
-  // communicator, and the tiles in flight on a GPU (~75 MB) stay inside the 126 MB L2.
-  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(256) << 10);
+  // size (plan_collective). 2 MiB per ring by default: 148 rings + header = 314 MiB per
+  // communicator (1.2 GB in round 1). Measured at 4 and 8 GPUs (profiles/r2): 2 MiB rings are
+  // 3-10 % faster than 1 MiB ones on reduce / broadcast (eight 64 KiB tiles in flight also
+  // for the layouts that double or n-fold a slot), 4 MiB rings add nothing.
+  c->slot_bytes = c->cfg.slot_bytes ? round_up_sz(c->cfg.slot_bytes, 4096) : (size_t(512) << 10);
   c->ring_bytes = c->slot_bytes * PDCC_RING_DEPTH;
   c->max_blocks = c->cfg.max_blocks > 0 ? c->cfg.max_blocks : PDCC_MAX_BLOCKS;
   if (c->max_blocks > PDCC_MAX_BLOCKS) c->max_blocks = PDCC_MAX_BLOCKS;
@@ -877,7 +879,7 @@ int pdcc_plan_dry(int nranks, int has_multicast, size_t slot_bytes, int rings, c
   memset(&dev, 0, sizeof(dev));
   dev.rank = 0;
   dev.nranks = nranks;
-  dev.ring_bytes = uint32_t((slot_bytes ? slot_bytes : (size_t(256) << 10)) * PDCC_RING_DEPTH);
+  dev.ring_bytes = uint32_t((slot_bytes ? slot_bytes : (size_t(512) << 10)) * PDCC_RING_DEPTH);
   dev.mc = has_multicast ? reinterpret_cast<char*>(uintptr_t(16)) : nullptr;  // never dereferenced
   Plan p;
   int rc = plan_collective(dev, rings > 0 ? rings : PDCC_MAX_BLOCKS, has_multicast != 0, *op, &p);
@@ -1096,6 +1098,12 @@ static int try_symmetric(pdcc_comm* c, const pdcc_op_t& op, void* stream, int* t
   }
   // tiny messages stay on the flag-in-data kernels (two barriers cost more than they do)
   if (!forced && bytes <= sym_min_bytes(n)) return PDCC_OK;
+  // Measured (bench.py "symmetric_memory", profiles/r2): below four ranks the staged push
+  // kernels beat the switch for everything but all_gather (2 GPUs, 256 MiB: all_reduce 0.53 ms
+  // staged vs 0.71 zero-copy); a large broadcast is better off with the staged two-phase
+  // kernel at every group size (8 GPUs, 64 MiB: 161 vs 193 us).
+  if (!forced && n < 4 && op.coll != PDCC_ALL_GATHER) return PDCC_OK;
+  if (!forced && op.coll == PDCC_BROADCAST && bytes >= (uint64_t(16) << 20)) return PDCC_OK;
   *taken = 1;
   return launch_sym(c->dev, ring_limit(c), op, in, out, stream);
 }

@@ -115,7 +115,7 @@ typedef struct {
   int device_timeout_ms;  /* device-side flag wait timeout (0 = default 10 s) */
   size_t slot_bytes;      /* a CTA's ring is PDCC_RING_DEPTH x this; every call
                              cuts the ring into slots for its own tile size
-                             (0 = default 256 KiB, i.e. 1 MiB rings)          */
+                             (0 = default 512 KiB, i.e. 2 MiB rings)          */
   int max_blocks;         /* rings to provision (0 = PDCC_MAX_BLOCKS)         */
   size_t heap_bytes;      /* symmetric heap for zero-copy tensors (0 = none)  */
   char key[64];           /* unique per group: namespaces the store keys      */

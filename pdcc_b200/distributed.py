@@ -452,7 +452,7 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op: bool = False):
 
 
 def all_reduce_avg(tensor, out=None, group=None, async_op: bool = False, scale=None,
-                   nblocks: int = 0):
+                   nblocks: int = 0, algo=None):
     """K2 — the README's "send all gradients to all GPUs, average them" (README.md:5) as one
     kernel: sum over ranks, multiply by 1/world_size (or `scale`), optionally write fp32
     from a bf16/fp16 input. `out=None` averages in place."""
@@ -468,7 +468,7 @@ def all_reduce_avg(tensor, out=None, group=None, async_op: bool = False, scale=N
         if g.size() > 1:
             # nblocks caps the CTAs of the kernel: an average that overlaps a backward pass
             # should leave most SMs to the GEMMs (parallel/data_parallel.py)
-            native_comm(g).all_reduce(tensor, K.SUM, out=out, scale=s, nblocks=nblocks)
+            native_comm(g).all_reduce(tensor, K.SUM, out=out, scale=s, nblocks=nblocks, algo=algo)
         elif out is not None or s != 1.0:
             K.local_scale_cast(tensor if out is None else out, tensor, s)
         return _finish(async_op, True)

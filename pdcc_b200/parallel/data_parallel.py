@@ -116,12 +116,14 @@ class BucketedGradAverager:
         if self.world == 1:
             return
         if self._stream is None:
-            dist.all_reduce_avg(b.flat, group=self.group, nblocks=self._ctas(b))
+            dist.all_reduce_avg(b.flat, group=self.group, nblocks=self._ctas(b),
+                                algo="sym" if b.symmetric else None)
             return
         b.ready.record()  # on the compute stream: this bucket's gradients are complete
         self._stream.wait_event(b.ready)
         with torch.cuda.stream(self._stream):
-            dist.all_reduce_avg(b.flat, group=self.group, nblocks=self._ctas(b))
+            dist.all_reduce_avg(b.flat, group=self.group, nblocks=self._ctas(b),
+                                algo="sym" if b.symmetric else None)
             b.done.record()
 
     def zero_grad(self) -> None:
