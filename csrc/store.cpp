@@ -152,6 +152,13 @@ struct pdcc_store_server {
           (olen && !send_all(fd, out.data(), olen)) || !send_all(fd, &num, 8))
         break;
     }
+    {
+      // forget the descriptor before closing it: server_stop must never shutdown() a number
+      // the process has meanwhile reused for something else
+      std::lock_guard<std::mutex> g(mu);
+      for (auto& c : client_fds)
+        if (c == fd) c = -1;
+    }
     ::close(fd);
   }
 
@@ -258,7 +265,8 @@ int pdcc_store_server_stop(pdcc_store_server_t* s) {
   if (s->accept_thread.joinable()) s->accept_thread.join();
   {
     std::lock_guard<std::mutex> g(s->mu);
-    for (int fd : s->client_fds) ::shutdown(fd, SHUT_RDWR);
+    for (int fd : s->client_fds)
+      if (fd >= 0) ::shutdown(fd, SHUT_RDWR);
     s->cv.notify_all();
   }
   for (auto& t : s->workers)

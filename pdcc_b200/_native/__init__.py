@@ -210,7 +210,15 @@ class Store:
         if serve:
             srv = C.c_void_p()
             bound = C.c_int()
-            check(L.pdcc_store_server_start(b"", port, C.byref(srv), C.byref(bound)))
+            # bind where the clients will connect (loopback for the usual 127.0.0.1), not on
+            # every interface: the store is unauthenticated
+            import socket
+
+            try:
+                bind = socket.gethostbyname(host)
+            except OSError:
+                bind = ""
+            check(L.pdcc_store_server_start(bind.encode(), port, C.byref(srv), C.byref(bound)))
             self._server = srv
             self.port = bound.value
         cl = C.c_void_p()

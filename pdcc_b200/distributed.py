@@ -195,14 +195,29 @@ def destroy_process_group(group: Optional[Group] = None) -> None:
     never does this (main.py:90-95); exiting without it is also safe."""
     if not is_initialized():
         return
+    def _quiesce(pg) -> None:
+        # A peer's kernel may still be posting its last flags into this rank's block: every
+        # member finishes its device work and meets at a host barrier BEFORE anyone unmaps or
+        # frees (on the legacy-IPC path the owner's cudaFree could otherwise hand the memory
+        # to the next cudaMalloc while a peer still writes into it).
+        if torch.cuda.is_available():
+            torch.cuda.synchronize()
+        try:
+            tdist.barrier(group=pg)
+        except Exception:
+            pass
+
     if group is not None and group is not GroupMember.WORLD:
         if isinstance(group, Group):
             if group.comm is not None:
+                _quiesce(group.torch_pg)
                 group.comm.destroy()
                 group.comm = None
             if group in _S.groups:
                 _S.groups.remove(group)
         return
+    if any(g.comm is not None for g in _S.groups):
+        _quiesce(None)
     for g in _S.groups:
         if g.comm is not None:
             g.comm.destroy()

@@ -103,3 +103,39 @@ def test_demos_world1_b200(name, tmp_path):
         assert res.item() == want[name]
     elif name in ("do_gather", "do_all_gather"):
         assert [t.item() for t in res] == [0.0]
+
+
+def test_named_c_abi_entry_points_once_each():
+    """pdcc_all_reduce ... pdcc_barrier (include/pdcc.h) called straight through ctypes on a
+    one-rank communicator: the call shapes of main.py:14,23,37,52,68,81 as a C host program
+    would make them."""
+    import ctypes as C
+
+    L = N.lib()
+    comm = K.NativeComm(None, "cabi", 0, 1, 0)
+    h, st = comm._h, torch.cuda.current_stream().cuda_stream
+    n = 70001
+    try:
+        x = torch.arange(n, dtype=torch.float32, device="cuda")
+        want = x.clone()
+        N.check(L.pdcc_all_reduce(h, x.data_ptr(), n, N.F32, K.SUM, st))
+        N.check(L.pdcc_reduce(h, x.data_ptr(), n, N.F32, K.MAX, 0, st))
+        N.check(L.pdcc_broadcast(h, x.data_ptr(), n, N.F32, 0, st))
+        out = torch.zeros(n, device="cuda")
+        N.check(L.pdcc_all_reduce_scaled(h, x.data_ptr(), out.data_ptr(), n, N.F32, N.F32, 0.5, st))
+        lst = (C.c_void_p * 1)(x.data_ptr())
+        sc = torch.zeros(n, device="cuda")
+        N.check(L.pdcc_scatter(h, sc.data_ptr(), lst, n, N.F32, 0, st))
+        ga = torch.zeros(n, device="cuda")
+        glst = (C.c_void_p * 1)(ga.data_ptr())
+        N.check(L.pdcc_gather(h, x.data_ptr(), glst, n, N.F32, 0, st))
+        ag = torch.zeros(n, device="cuda")
+        alst = (C.c_void_p * 1)(ag.data_ptr())
+        N.check(L.pdcc_all_gather(h, alst, x.data_ptr(), n, N.F32, st))
+        N.check(L.pdcc_barrier(h, st))
+        comm.check()
+        assert torch.equal(x, want) and torch.equal(sc, want) and torch.equal(ga, want)
+        assert torch.equal(ag, want)
+        torch.testing.assert_close(out, want * 0.5)
+    finally:
+        comm.destroy()
