@@ -160,9 +160,8 @@ struct Ctx {
   size_t ring_off;
   uint32_t slot_stride;
   int depth;
-  // The warp group this thread works in (run_pipeline gives every pipeline stage its own
-  // group). Stage code strides its loops by (tid, nt); group-wide synchronisation uses the
-  // named barrier `bar`.
+  // The worker group this thread belongs to (run_pipeline gives every pipeline stage its own
+  // group): stage code strides its loops by (tid, nt). `bar` is the group's index + 1.
   int tid, nt, bar;
 
   __device__ __forceinline__ size_t slot_off(int t) const {
@@ -175,11 +174,6 @@ struct Ctx {
   __device__ __forceinline__ char* mine(size_t off) const { return a->comm.base[rank] + off; }
   __device__ __forceinline__ char* mc(size_t off) const { return a->comm.mc + off; }
 };
-
-// Named-barrier sync of the current warp group (all of its c.nt threads call).
-__device__ __forceinline__ void group_sync(const Ctx& c) {
-  asm volatile("bar.sync %0, %1;" ::"r"(c.bar), "r"(c.nt) : "memory");
-}
 
 __device__ __forceinline__ int flag_index(int chan, int b, int src) {
   return (chan * PDCC_MAX_BLOCKS + b) * PDCC_MAX_RANKS + src;

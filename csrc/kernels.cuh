@@ -15,12 +15,12 @@
 // consecutive calls of different collectives follow each other with no end-of-kernel
 // barrier and no host-side epoch (launches are CUDA-graph capturable).
 //
-// run_pipeline() gives every stage its OWN group of warps and lets the three groups run
-// their tile loops independently: the only coupling between stages — on this rank and
-// across ranks alike — is the flags. While one group sits in the system-scope fence that
-// publishes its tile, the other two keep the links and HBM busy; IN runs up to `depth`
-// tiles ahead of OUT. Tiles are small (tens of KB per CTA) and rings are deep, so a
-// 256 MiB message is ~30-60 tiles per CTA and the pipeline fill is a few percent.
+// run_pipeline() gives every stage that has work on a rank its OWN group of worker warps and
+// lets the groups run their tile loops independently: the only coupling between stages — on
+// this rank and across ranks alike — is the flags. Two control warps keep every flag wait and
+// every system-scope fence off the data path (admitter / publisher, see run_pipeline below).
+// Tiles are small (64 KiB per CTA for large messages) and rings are deep (8-16 slots), so a
+// 256 MiB message is 28 tiles per CTA and IN runs up to `depth` tiles ahead of OUT.
 //
 // Reference parity: one kernel per torch.distributed call site of main.py (lines cited
 // at each policy). The reference itself has no kernels.

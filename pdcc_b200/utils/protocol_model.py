@@ -16,6 +16,12 @@ What is checked:
   * no write lands in a region while a read of an earlier tile's data is still in flight,
     or before every expected reader of that earlier data has read it.
 
+`pipeline="v4"` models the round-2 kernels: one agent per stage that has work on the rank, a
+publisher that raises every flag late (behind its fence) and raises the flags of idle stages
+on behalf of the stage before them, and the call-boundary guard of the first DEPTH tiles.
+(The model keeps DEPTH fixed; the kernels choose it per call, which only changes how far IN
+may run ahead.)
+
 It mirrors the protocol, not the CUDA source line by line: it validates the design (guards,
 flag semantics, team overlap, interleaving of different collectives on the same rings), which
 is the part that cannot be unit-tested on a GPU deterministically.
@@ -374,9 +380,107 @@ def cta(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int, t
     machine.epoch[(rank, ring)] = g0 + ntiles
 
 
+def cta_v4(machine: Machine, coll: Collective, rank: int, ring: int, ntiles: int,
+           rng: random.Random) -> Generator[None, None, None]:
+    """One CTA of pipeline v4 (round 2, csrc/kernels.cuh): every stage that has work on this
+    rank is an agent of its own that only waits for its input flags; a publisher agent raises
+    the flags some time AFTER the stage finished (its system fence takes 10-25 us), for all
+    stages at once, and raises the flag of a stage without work on behalf of the nearest
+    earlier stage that has work. The first DEPTH tiles of a call wait until every rank has
+    finished everything that came before on the ring."""
+    if coll.ll:
+        yield from cta(machine, coll, rank, ring, ntiles)
+        return
+    n = machine.n
+    g0 = machine.epoch.get((rank, ring), 0)
+    readers = _expected_readers(coll, n)
+    everyone = _all(n)
+    fns = [coll.in_, coll.mid, coll.out if coll.has_out else (lambda r: None)]
+    has = [f(rank) is not None for f in fns]
+    if not any(has):
+        has[0] = True  # a rank with no work still takes part in the flag chain
+    finished = [0, 0, 0]
+    # v4 rule (kernels.cuh, ready_from()): a rank whose IN stage touches no slot raises no
+    # READY, so nobody lists it (in the kernels the root of a gather does have an IN stage, a
+    # local copy outside the slots; leaving it out here is the same thing)
+    ready_from = [s for s in coll.ready_from(rank) if coll.in_(s) is not None]
+
+    def wait(chan, val, srcs):
+        if chan == DONE and machine.no_guard:
+            return
+        while any(machine.get_flag(chan, rank, ring, s) < val for s in srcs):
+            yield
+
+    def run_stage(st, g):
+        if st is None:
+            return
+        for (rk, region, writer) in st.reads:
+            machine.begin_read(rank, rk, ring, g, region, writer)
+        for (rk, region) in st.writes:
+            machine.begin_write(rank, rk, ring, g, region, readers.get((rk, region), set()))
+        yield
+        for (rk, region, _w) in st.reads:
+            machine.end_read(rank, rk, ring, g, region)
+        for (rk, region) in st.writes:
+            machine.end_write(rk, ring, g, region)
+
+    def agent(stage):
+        for t in range(ntiles):
+            g = g0 + t
+            if stage == 0:
+                yield from wait(DONE, g0 if t < DEPTH else g - DEPTH + 1, everyone)
+            elif stage == 1:
+                yield from wait(READY, g + 1, ready_from)
+            else:
+                yield from wait(MID, g + 1, everyone)
+            yield from run_stage(fns[stage](rank), g)
+            finished[stage] = t + 1
+            yield
+
+    def publisher():
+        pub = [0, 0, 0]
+        out_on = coll.has_out and has[2]
+        while any(has[s] and pub[s] < ntiles for s in range(3)):
+            snap = list(finished)
+            for _ in range(rng.randint(0, 3)):  # the fence: flags lag the data
+                yield
+            def post(chan, val, dsts):
+                for d in dsts:
+                    machine.post(chan, d, ring, rank, val)
+            if has[0] and snap[0] > pub[0]:
+                v = g0 + snap[0]
+                post(READY, v, coll.ready_to(rank))
+                if coll.has_out and not has[1]:
+                    post(MID, v, everyone)
+                if not has[1] and not out_on:
+                    post(DONE, v, everyone)
+                pub[0] = snap[0]
+            if has[1] and snap[1] > pub[1]:
+                v = g0 + snap[1]
+                if coll.has_out:
+                    post(MID, v, everyone)
+                if not out_on:
+                    post(DONE, v, everyone)
+                pub[1] = snap[1]
+            if out_on and snap[2] > pub[2]:
+                post(DONE, g0 + snap[2], everyone)
+                pub[2] = snap[2]
+            yield
+
+    gens = [agent(s) for s in range(3) if has[s] and (s < 2 or coll.has_out)] + [publisher()]
+    while gens:
+        x = rng.choice(gens)
+        try:
+            next(x)
+        except StopIteration:
+            gens.remove(x)
+        yield
+    machine.epoch[(rank, ring)] = g0 + ntiles
+
+
 def run_sequence(n: int, rings: int, calls: List[Tuple[Collective, int, int]], seed: int,
                  teams: bool = True, max_steps: int = 2_000_000, no_guard: bool = False,
-                 early_ready: bool = False) -> int:
+                 early_ready: bool = False, pipeline: str = "v2") -> int:
     """Runs `calls` = [(collective, ntiles, nrings_used)] back to back on every rank with a random
     scheduler. A rank starts call k+1 on a ring as soon as ITS call k on that ring is done (stream
     order), regardless of the other ranks. Returns the number of scheduler steps."""
@@ -399,7 +503,8 @@ def run_sequence(n: int, rings: int, calls: List[Tuple[Collective, int, int]], s
         k = rng.choice(keys)
         if active[k] is None:
             coll, ntiles = queues[k].pop(0)
-            active[k] = cta(m, coll, k[0], k[1], ntiles, teams, early_ready)
+            active[k] = (cta_v4(m, coll, k[0], k[1], ntiles, rng) if pipeline == "v4"
+                         else cta(m, coll, k[0], k[1], ntiles, teams, early_ready))
         before = (dict(m.flag), {kk: (v["tile"], v["writing"], v["reading"]) for kk, v in m.mem.items()})
         try:
             next(active[k])

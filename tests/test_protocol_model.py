@@ -57,3 +57,30 @@ def test_early_ready_variant_is_also_safe():
     for seed in range(8):
         calls = [(rng.choice(colls), rng.choice([1, 2, 4, 7]), 1) for _ in range(8)]
         pm.run_sequence(n, 1, calls, seed, early_ready=True)
+
+
+@pytest.mark.parametrize("n", [2, 3, 4])
+def test_pipeline_v4_independent_stages_and_late_flags(n):
+    """The round-2 kernels (csrc/kernels.cuh, pipeline v4): one agent per stage, flags raised
+    late by a publisher, idle stages' flags raised by the stage before them. Alone with slot
+    reuse, and in mixed sequences that also contain LL calls."""
+    colls = _collectives(n)
+    for coll in colls:
+        for ntiles in (1, 3, 9):
+            for seed in range(3):
+                pm.run_sequence(n, 1, [(coll, ntiles, 1)], seed, pipeline="v4")
+    rng = random.Random(5)
+    for seed in range(10):
+        calls = [(rng.choice(colls), rng.choice([1, 2, 3, 6, 9]), rng.choice([1, 2])) for _ in range(10)]
+        pm.run_sequence(n, 2, calls, seed, pipeline="v4")
+
+
+def test_pipeline_v4_checker_catches_a_missing_slot_guard():
+    n, caught = 3, 0
+    for seed in range(40):
+        try:
+            pm.run_sequence(n, 1, [(pm.all_reduce_twoshot(n), 9, 1), (pm.broadcast_push(n, 0), 9, 1)],
+                            seed, no_guard=True, pipeline="v4")
+        except pm.ProtocolError:
+            caught += 1
+    assert caught > 0
