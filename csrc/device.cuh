@@ -390,20 +390,27 @@ __device__ __noinline__ void deal16(char* const* __restrict__ base, int first, i
                                     int skip, size_t dst_off, size_t part_stride,
                                     const char* __restrict__ s, size_t n16, size_t sub16, int tid,
                                     int nt) {
-  for (size_t i = tid; i < n16; i += size_t(nt) * UNROLL) {
+  // j / sub16 as a multiply-high: exact while j * sub16 < 2^32 (a tile is at most a few
+  // thousand units, a part a fraction of that), and free of the division's registers
+  const uint32_t n32 = uint32_t(n16), s32 = uint32_t(sub16);
+  const uint32_t magic = uint32_t(((uint64_t(1) << 32) + s32 - 1) / s32);
+  for (uint32_t i = uint32_t(tid); i < n32; i += uint32_t(nt) * UNROLL) {
     uint4 v[UNROLL];
 #pragma unroll
     for (int k = 0; k < UNROLL; ++k) {
-      const size_t j = i + size_t(k) * nt;
-      if (j < n16) v[k] = ld_stream_v4(s + (j << 4));
+      const uint32_t j = i + uint32_t(k) * uint32_t(nt);
+      if (j < n32) v[k] = ld_stream_v4(s + (size_t(j) << 4));
     }
 #pragma unroll
     for (int k = 0; k < UNROLL; ++k) {
-      const size_t j = i + size_t(k) * nt;
-      if (j < n16) {
-        const uint32_t o = uint32_t(j) / uint32_t(sub16);  // a tile is far below 2^32 units
-        const int r = (first + int(o)) % nranks;
-        if (r != skip) st_v4(base[r] + dst_off + o * part_stride + ((j - o * sub16) << 4), v[k]);
+      const uint32_t j = i + uint32_t(k) * uint32_t(nt);
+      if (j < n32) {
+        const uint32_t o = s32 == 1 ? j : __umulhi(j, magic);
+        int r = first + int(o);
+        if (r >= nranks) r -= nranks;  // first <= nranks and o < nranks
+        if (r >= nranks) r -= nranks;
+        if (r != skip)
+          st_v4(base[r] + dst_off + size_t(o) * part_stride + (size_t(j - o * s32) << 4), v[k]);
       }
     }
   }
