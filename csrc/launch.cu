@@ -104,6 +104,9 @@ struct PlanEnv {
   int threads;            // PDCC_THREADS           threads per CTA of the pipeline kernels (0 = auto)
   int copy_tma;           // PDCC_COPY_TMA          local copies through the TMA engine (default 1)
   int trace;              // PDCC_TRACE             CTA 0 records a timeline (pdcc_comm_read_trace)
+  int copy_chunk_kb;      // PDCC_COPY_CHUNK_KB     TMA local copy: KiB per bulk copy
+  int copy_stages;        // PDCC_COPY_STAGES       .. stages of the shared-memory ring
+  int copy_ctas_per_sm;   // PDCC_COPY_CTAS_PER_SM  .. CTAs per SM
 };
 static PlanEnv g_plan_env;
 static std::atomic<int> g_plan_env_state{0};  // 0 = not read, 1 = valid
@@ -120,6 +123,9 @@ static void read_plan_env(PlanEnv* e) {
   e->threads = env_int("PDCC_THREADS", 0);
   e->copy_tma = env_int("PDCC_COPY_TMA", 1);
   e->trace = env_int("PDCC_TRACE", 0);
+  e->copy_chunk_kb = env_int("PDCC_COPY_CHUNK_KB", int(kTmaChunk >> 10));
+  e->copy_stages = env_int("PDCC_COPY_STAGES", kTmaStages);
+  e->copy_ctas_per_sm = env_int("PDCC_COPY_CTAS_PER_SM", 1);
 }
 
 static const PlanEnv& plan_env() {
@@ -705,24 +711,32 @@ int pdcc_local_copy(void* dst, const void* src, uint64_t bytes, int device, void
   const bool tma_ok = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src) | bytes) & 15u) == 0 &&
                       bytes >= (uint64_t(1) << 20) && plan_env().copy_tma != 0;
   if (tma_ok) {
-    // big aligned copies go through the TMA engine (tma_copy.cuh), two CTAs per SM
+    // big aligned copies go through the TMA engine (tma_copy.cuh), one CTA per SM
     static bool attr_set[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
       e = cudaFuncSetAttribute(tma_copy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               int(kTmaSmemBytes));
+                               int(kTmaMaxSmemBytes));
       if (e != cudaSuccess) {
         set_error("tma_copy attribute: %s", cudaGetErrorString(e));
         return PDCC_ECUDA;
       }
       attr_set[dev] = true;
     }
-    uint64_t chunks = (bytes + kTmaChunk - 1) / kTmaChunk;
-    uint64_t blocks = chunks < 2 * 148 ? chunks : 2 * 148;
-    tma_copy_kernel<<<dim3(unsigned(blocks)), dim3(32), kTmaSmemBytes,
+    const PlanEnv& pe = plan_env();
+    uint32_t chunk = uint32_t(pe.copy_chunk_kb > 0 ? pe.copy_chunk_kb : 16) << 10;
+    int stages = pe.copy_stages > 1 ? pe.copy_stages : 2;
+    if (stages > kTmaMaxStages) stages = kTmaMaxStages;
+    while (uint64_t(chunk) * stages > kTmaMaxSmemBytes && stages > 2) --stages;
+    if (uint64_t(chunk) * stages > kTmaMaxSmemBytes) chunk = (kTmaMaxSmemBytes / stages) & ~uint32_t(1023);
+    const uint64_t per_sm = uint64_t(pe.copy_ctas_per_sm > 0 ? pe.copy_ctas_per_sm : 1);
+    uint64_t chunks = (bytes + chunk - 1) / chunk;
+    uint64_t blocks = chunks < per_sm * 148 ? chunks : per_sm * 148;
+    tma_copy_kernel<<<dim3(unsigned(blocks)), dim3(32), size_t(chunk) * stages,
                       static_cast<cudaStream_t>(stream)>>>(static_cast<char*>(dst),
-                                                           static_cast<const char*>(src), bytes);
+                                                           static_cast<const char*>(src), bytes,
+                                                           chunk, stages);
   } else {
     uint64_t blocks = (bytes + (64 << 10) - 1) / (64 << 10);
     if (blocks > 4 * 148) blocks = 4 * 148;

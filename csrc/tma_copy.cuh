@@ -12,9 +12,13 @@
 
 namespace pdcc {
 
-constexpr int kTmaStages = 6;
-constexpr uint32_t kTmaChunk = 16 * 1024;                  // bytes per bulk copy
-constexpr uint32_t kTmaSmemBytes = kTmaStages * kTmaChunk;  // 96 KiB: two CTAs per SM
+constexpr int kTmaMaxStages = 16;
+// Defaults from benchmarks/copy_sweep.py (profiles/r2/copy_sweep_1gpu.jsonl, 256 MiB fp32):
+// 4 x 16 KiB stages, ONE CTA per SM: 0.0848 ms = 6.33 TB/s (0.97 of the measured copy peak;
+// torch's D2D copy 0.0843 ms). Deeper or wider is slower: 6 stages x 2 CTAs/SM 0.0927 ms.
+constexpr int kTmaStages = 4;
+constexpr uint32_t kTmaChunk = 16 * 1024;
+constexpr uint32_t kTmaMaxSmemBytes = 200 * 1024;           // what the launcher opts in to
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -60,12 +64,17 @@ __device__ __forceinline__ void bulk_store(void* gdst, const void* smem_src, uin
 // dst, src 16-byte aligned; bytes a multiple of 16. Chunk k of CTA b is chunk k*grid + b of
 // the buffer, so all CTAs stream through the same region of HBM at the same time and finish
 // together.
+// chunk_bytes (a multiple of 16) and nstages (<= kTmaMaxStages) are launch parameters: the
+// dynamic shared memory of the launch is nstages * chunk_bytes.
 __global__ void __launch_bounds__(32) tma_copy_kernel(char* __restrict__ dst,
                                                       const char* __restrict__ src,
-                                                      uint64_t bytes) {
+                                                      uint64_t bytes, uint32_t chunk_bytes,
+                                                      int nstages) {
   extern __shared__ __align__(128) unsigned char stage_mem[];
-  __shared__ __align__(8) uint64_t bars[kTmaStages];
+  __shared__ __align__(8) uint64_t bars[kTmaMaxStages];
   if (threadIdx.x != 0) return;
+  const uint32_t kTmaChunk = chunk_bytes;  // shadows the default: same loop as before
+  const int kTmaStages = nstages;
 
   const uint64_t nchunks = (bytes + kTmaChunk - 1) / kTmaChunk;
   if (blockIdx.x >= nchunks) return;
