@@ -59,7 +59,7 @@ def main() -> None:
     ap.add_argument("--subgroup", default="", help="comma list of global ranks, e.g. 1,3")
     ap.add_argument("--sizes", default="", help="explicit comma list of sizes (overrides min/max/factor)")
     ap.add_argument("--env-sweep", default="",
-                    help="A/B a planner knob inside ONE job, e.g. PDCC_TILE_SPLIT=0,1,4,8 "
+                    help="A/B a planner knob inside ONE job, e.g. PDCC_TILE_BYTES=32768,65536 "
                          "(the native planner reads its knobs from the environment per call)")
     ap.add_argument("--jobs-file", default="",
                     help="JSON list of dicts, each overriding options (colls, sizes, dtype, op, "
