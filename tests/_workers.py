@@ -476,6 +476,9 @@ def api_misc(rank, size):
     else:
         res["sentinel_rank"] = dist.get_rank(g)
         res["sentinel_size"] = dist.get_world_size(g)
+    # symmetric memory degrades to ordinary tensors where there is nothing to gain (gloo, CPU)
+    sym = dist.empty_symmetric(3, 5, dtype=torch.float64)
+    res["sym_fallback"] = (tuple(sym.shape), str(sym.dtype), dist.is_symmetric(sym))
     try:
         dist.all_reduce(torch.zeros(1), op=17)
     except ValueError as e:

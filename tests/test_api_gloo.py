@@ -19,6 +19,7 @@ def test_api_misc(tmp_path):
         assert "unsupported reduce op" in res[r]["bad_op"]
         assert "Invalid process group" in res[r]["bad_group"]
         assert "init_process_group('b200'" in res[r]["native_on_gloo"]
+        assert res[r]["sym_fallback"] == ((3, 5), "torch.float64", False)
     for r in (0, n - 1):
         assert res[r]["group_size"] == 2 and res[r]["group_rank"] == (0 if r == 0 else 1)
         assert res[r]["global_of_1"] == n - 1 and res[r]["group_of_last"] == 1

@@ -21,9 +21,26 @@ def test_header_and_binding_agree():
     assert f"#define PDCC_MAX_BLOCKS {N.MAX_BLOCKS}" in text
     assert f"#define PDCC_RING_DEPTH {N.RING_DEPTH}" in text
     for name in ("pdcc_all_reduce", "pdcc_reduce", "pdcc_broadcast", "pdcc_scatter", "pdcc_gather",
-                 "pdcc_all_gather", "pdcc_collective", "pdcc_emu_collective"):
+                 "pdcc_all_gather", "pdcc_collective", "pdcc_emu_collective", "pdcc_sym_alloc",
+                 "pdcc_sym_query", "pdcc_comm_read_trace", "pdcc_reload_env",
+                 "pdcc_emu2_all_reduce_noalloc", "pdcc_emu2_noalloc_check"):
         assert name in text and hasattr(N.lib(), name)
+    assert "PDCC_ALGO_SYM = 9" in text and N.ALGO_NAMES["sym"] == 9
     assert C.sizeof(N.Op) == 4 * 8 + 8 + 8 + 8 + 8 * N.MAX_RANKS
+
+
+def test_planner_knobs_are_cached_until_reloaded(monkeypatch):
+    """The planner reads PDCC_* once; pdcc_reload_env re-reads (benchmarks A/B a knob in one job)."""
+    base = N.plan_dry(8, N.ALL_REDUCE, 64 << 20, N.F32)
+    monkeypatch.setenv("PDCC_TILE_BYTES", "32768")
+    assert N.plan_dry(8, N.ALL_REDUCE, 64 << 20, N.F32)["tile_bytes"] == base["tile_bytes"]
+    N.reload_env()
+    try:
+        assert N.plan_dry(8, N.ALL_REDUCE, 64 << 20, N.F32)["tile_bytes"] == 32768
+    finally:
+        monkeypatch.delenv("PDCC_TILE_BYTES")
+        N.reload_env()
+    assert N.plan_dry(8, N.ALL_REDUCE, 64 << 20, N.F32) == base
 
 
 def test_dtype_codes():
