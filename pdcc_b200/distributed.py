@@ -207,10 +207,18 @@ def destroy_process_group(group: Optional[Group] = None) -> None:
         except Exception:
             pass
 
+    def _report(comm) -> None:
+        # last chance to tell the user that some kernel gave up waiting for a peer
+        try:
+            comm.check()
+        except Exception as e:  # noqa: BLE001 - teardown must go on
+            warnings.warn(f"pdcc_b200: {e}")
+
     if group is not None and group is not GroupMember.WORLD:
         if isinstance(group, Group):
             if group.comm is not None:
                 _quiesce(group.torch_pg)
+                _report(group.comm)
                 group.comm.destroy()
                 group.comm = None
             if group in _S.groups:
@@ -220,6 +228,7 @@ def destroy_process_group(group: Optional[Group] = None) -> None:
         _quiesce(None)
     for g in _S.groups:
         if g.comm is not None:
+            _report(g.comm)
             g.comm.destroy()
             g.comm = None
     if _S.store is not None:
