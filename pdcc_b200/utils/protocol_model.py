@@ -518,3 +518,48 @@ def run_sequence(n: int, rings: int, calls: List[Tuple[Collective, int, int]], s
                                 f"(pending: {[kk for kk in keys][:8]})")
         if steps > max_steps:
             raise ProtocolError("step budget exceeded")
+
+
+def run_sym_barriers(n: int, ncalls: int, seed: int) -> int:
+    """Model of the two arrival-counter barriers of the zero-copy kernels (csrc/sym.cuh) for
+    ONE CTA index: per call every rank adds 1 to the `enter` counter of all ranks
+    (multimem.red.add), waits until its own copy reaches (epoch + 1) * n, works, does the same
+    on the `exit` counter, then bumps its local epoch. Counters never reset. Checked under a
+    random schedule: nobody works in call k before every rank has entered call k, and nobody
+    leaves call k before every rank has finished working in it. Returns the steps taken."""
+    rng = random.Random(seed)
+    counter = [[0, 0] for _ in range(n)]          # [rank][phase]
+    entered = [0] * n                             # calls rank r has entered (arrived at enter)
+    worked = [0] * n                              # calls rank r has finished working in
+
+    def rank_prog(r):
+        for k in range(ncalls):
+            for q in range(n):
+                counter[q][0] += 1
+            entered[r] = k + 1
+            yield
+            while counter[r][0] < (k + 1) * n:
+                yield
+            if min(entered) < k + 1:
+                raise ProtocolError(f"rank {r} works in call {k} before everyone entered it")
+            yield                                  # the work
+            worked[r] = k + 1
+            for q in range(n):
+                counter[q][1] += 1
+            yield
+            while counter[r][1] < (k + 1) * n:
+                yield
+            if min(worked) < k + 1:
+                raise ProtocolError(f"rank {r} leaves call {k} before everyone finished it")
+    gens = [rank_prog(r) for r in range(n)]
+    steps = 0
+    while gens:
+        g = rng.choice(gens)
+        try:
+            next(g)
+        except StopIteration:
+            gens.remove(g)
+        steps += 1
+        if steps > 1_000_000:
+            raise ProtocolError("sym barrier model: no progress")
+    return steps

@@ -84,3 +84,10 @@ def test_pipeline_v4_checker_catches_a_missing_slot_guard():
         except pm.ProtocolError:
             caught += 1
     assert caught > 0
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+def test_zero_copy_arrival_counter_barriers(n):
+    """csrc/sym.cuh: never-reset arrival counters with target (epoch + 1) * n keep calls apart."""
+    for seed in range(20):
+        pm.run_sym_barriers(n, 6, seed)
